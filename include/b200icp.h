@@ -1,0 +1,123 @@
+/* b200icp.h -- C ABI of libb200icp.so, the B200 (sm_100a) batched ICP engine.
+ *
+ * This is the drop-in boundary for the reference's ICP hot path
+ * (fadli0029/LiDAR-SLAM).  Each entry point names the reference interface it
+ * replaces.  Plain pointers and sizes only; no torch / C++ types.
+ *
+ * Ownership: the caller allocates and frees EVERY buffer (device memory unless
+ * stated otherwise), including the workspace.  The library keeps no global
+ * state, never allocates device memory, and is re-entrant.  All launches are
+ * asynchronous on the given CUDA stream (pass a cudaStream_t cast to void*;
+ * NULL = the legacy default stream).  Functions return 0 or a negative
+ * B200ICP_ERR_* code; per-pair anomalies are reported in `status_out`, never
+ * as a call failure, because the reference does not raise on them either.
+ */
+#ifndef B200ICP_H_
+#define B200ICP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ICP_VERSION 100 /* 0.1.0 */
+
+/* ---- call-level error codes ------------------------------------------------ */
+#define B200ICP_OK 0
+#define B200ICP_ERR_BAD_ARG (-1)   /* null pointer, non-positive size, bad dim        */
+#define B200ICP_ERR_TOO_LARGE (-2) /* n_max beyond what this build supports           */
+#define B200ICP_ERR_WORKSPACE (-3) /* workspace smaller than b200icp_workspace_bytes  */
+#define B200ICP_ERR_CUDA (-4)      /* launch failed; see cudaGetLastError             */
+#define B200ICP_ERR_NO_DEVICE (-5) /* no sm_100 device / wrong architecture           */
+
+/* ---- per-pair status (status_out) --------------------------------------------
+ * Which of the reference's three stop tests fired (modules/icp.py:172-178), or
+ * why the pair was not run. */
+#define B200ICP_STATUS_EPSILON 0   /* error < epsilon                      icp.py:172 */
+#define B200ICP_STATUS_MAX_ITERS 1 /* iteration >= max_iters               icp.py:174 */
+#define B200ICP_STATUS_STALLED 2   /* |last_err - error| < stopping_thresh icp.py:177 */
+#define B200ICP_STATUS_NONFINITE 3 /* error became NaN/Inf; stopped early             */
+#define B200ICP_STATUS_EMPTY 4     /* source or target scan has no points; not run    */
+#define B200ICP_STATUS_NONPLANAR 5 /* 2-D entry given an init that moves points out of
+                                      the plane; not run (use the 3-D entry)           */
+#define B200ICP_STATUS_SKIPPED 6   /* pair index < 0 (padding entry); not run         */
+
+/* Library version (B200ICP_VERSION of the build). */
+int b200icp_version(void);
+
+/* Human-readable text for a B200ICP_ERR_* code (static storage). */
+const char* b200icp_error_string(int code);
+
+/* Bytes of device workspace b200icp_run needs for this problem size. */
+int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out);
+
+/* Batched point-to-point ICP.  Replaces, for every pair b independently,
+ *
+ *   run_icp(pc1, pc2, init_transform, epsilon, max_iters, stopping_thresh,
+ *           return_error=True, normalize_error, return_correspondences=True)
+ *                                                 -- modules/icp.py:123-189
+ *   (== code/icp_warm_up/icp.py:130-196), i.e. the loop of icp_iteration
+ *   (icp.py:100-121): transform, exact nearest neighbour (icp.py:29-41,161),
+ *   Kabsch solve (icp.py:43-74), compose, SSE / normalised error (icp.py:76-98),
+ *   and the three stop tests in the reference's order (icp.py:172-181).
+ *
+ * scans      [n_scans, n_max, dim] float64, row-major; scan i has counts[i] valid
+ *            leading points, the rest is ignored.  dim is 2 or 3.  16-byte aligned.
+ * counts     [n_scans] int32.
+ * pairs      [n_pairs, 2] int32: (source scan, target scan).  The source is moved
+ *            onto the target (pc1 -> pc2).  A negative source index skips the pair.
+ * init       [n_pairs, 4, 4] float64 row-major homogeneous initial transforms
+ *            (init_transform).  With dim == 2 it must keep z = 0 planar (what
+ *            TSE3_from_TSE2, modules/utils.py:227-240, produces).
+ * epsilon    [n_pairs] float64 (epsilon of each call; icp.py:127).
+ * normalize  [n_pairs] uint8 (normalize_error of each call; icp.py:131).
+ * max_iters, stopping_thresh: as icp.py:128-129 (same for the whole batch).
+ *
+ * T_out      [n_pairs, 4, 4] float64: transforms[-1] (icp.py:183-189).
+ * err_out    [n_pairs] float64: error of the last executed pass (describes the
+ *            transform BEFORE the final update, as in the reference).
+ * iters_out  [n_pairs] int32: number of executed passes (>= 1 when run).
+ * status_out [n_pairs] int32: B200ICP_STATUS_*.
+ * corr_out   [n_pairs, n_max] int32 or NULL: correspondences of the last pass
+ *            (index into the target scan; -1 beyond the source count).  Exact
+ *            float64 nearest neighbour; the lowest index wins exact ties.
+ * workspace  device scratch of at least b200icp_workspace_bytes(...) bytes.
+ */
+int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                const int32_t* pairs, const double* init, const double* epsilon,
+                const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* One exact nearest-neighbour pass, exposed on its own for tests and for the
+ * roofline measurement.  Replaces get_correspondences / KDTree.query
+ * (modules/icp.py:29-41 with :161) for a batch of (query set, target set) pairs
+ * taken from the same scan pool; queries are used as they are (no transform).
+ * corr_out [n_pairs, n_max] int32; dist2_out [n_pairs, n_max] float64 or NULL. */
+int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                    const int32_t* pairs, int n_pairs, int32_t* corr_out, double* dist2_out,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* FP32 FFMA issue-rate probe used as the roofline denominator: launches a
+ * register-only FFMA loop on every SM.  Performs `iters` * 64 dependent-free
+ * FFMAs per thread on a grid of n_blocks x 256 threads; the caller times it with
+ * CUDA events.  sink [n_blocks*256] float32 receives one value per thread so the
+ * loop cannot be removed. */
+int b200icp_ffma_probe(float* sink, int n_blocks, int iters, void* stream);
+
+/* Voxel-grid down-sampling on the device.  Replaces voxel_downsample
+ * (modules/icp.py:4-27): voxel index floor((p - min)/voxel_size), mean of the
+ * points in every occupied voxel, voxels in lexicographic (x, y, z) index order.
+ * points [n, 3] float64; out [n, 3] float64 (first *n_out rows written);
+ * n_out  device int32.  Workspace from b200icp_voxel_workspace_bytes. */
+int b200icp_voxel_workspace_bytes(int n_points, size_t* bytes_out);
+int b200icp_voxel_downsample(const double* points, int n_points, double voxel_size, double* out,
+                             int32_t* n_out, void* workspace, size_t workspace_bytes,
+                             void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ICP_H_ */

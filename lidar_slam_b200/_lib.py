@@ -1,0 +1,56 @@
+"""ctypes binding of libb200icp.so (the C ABI in include/b200icp.h).
+
+There is deliberately NO fallback: if the library is missing or cannot be
+loaded, using the engine raises.  Nothing here touches oracle/.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb200icp.so")
+
+c_int, c_double, c_size_t, c_void_p = ctypes.c_int, ctypes.c_double, ctypes.c_size_t, ctypes.c_void_p
+
+# name -> (restype, argtypes); mirrors include/b200icp.h exactly
+SIGNATURES = {
+    "b200icp_version": (c_int, []),
+    "b200icp_error_string": (ctypes.c_char_p, [c_int]),
+    "b200icp_workspace_bytes": (c_int, [c_int, c_int, c_int, ctypes.POINTER(c_size_t)]),
+    "b200icp_run": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                            c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                            c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200icp_nearest": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p,
+                                c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200icp_ffma_probe": (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    "b200icp_voxel_workspace_bytes": (c_int, [c_int, ctypes.POINTER(c_size_t)]),
+    "b200icp_voxel_downsample": (c_int, [c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p,
+                                         c_size_t, c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once).  Raises RuntimeError if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m lidar_slam_b200.build` "
+            "(nvcc, sm_100a).  There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if a declared symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str):
+    if code != 0:
+        msg = load().b200icp_error_string(code).decode()
+        raise RuntimeError(f"{what} failed: {msg} (code {code})")

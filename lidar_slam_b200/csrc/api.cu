@@ -1,0 +1,149 @@
+// extern "C" entry points of libb200icp.so (see include/b200icp.h).
+#include <cuda_runtime.h>
+
+#include "icp2d.cuh"
+#include "icp3d.cuh"
+
+using namespace b200icp;
+
+namespace {
+
+constexpr int kMax2d = 2048;  // 6-bit block id x 32 targets
+
+struct DeviceInfo {
+  int sms;
+  int ok;
+};
+DeviceInfo device_info() {
+  int dev = 0;
+  DeviceInfo d{0, 0};
+  if (cudaGetDevice(&dev) != cudaSuccess) return d;
+  int major = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
+  d.ok = (major == 10);
+  return d;
+}
+
+template <int R, int W, int MINB>
+int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
+  auto kern = icp2d_kernel<R, W, MINB>;
+  const Smem2dLayout L = smem2d_layout(p.n_max, W);
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
+    return B200ICP_ERR_CUDA;
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, L.total) != cudaSuccess || per_sm < 1)
+    return B200ICP_ERR_CUDA;
+  const long long resident = (long long)per_sm * sms;
+  const int grid = (int)(p.n_pairs < resident ? p.n_pairs : resident);
+  kern<<<grid, W * 32, L.total, stream>>>(p);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+
+int launch3d(const RunParams& p, int dim, cudaStream_t stream, int sms) {
+  constexpr int R = 6, TH = 256;
+  auto kern = icp3d_kernel<R, TH>;
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TH, 0) != cudaSuccess || per_sm < 1)
+    return B200ICP_ERR_CUDA;
+  const long long resident = (long long)per_sm * sms;
+  const int grid = (int)(p.n_pairs < resident ? p.n_pairs : resident);
+  kern<<<grid, TH, 0, stream>>>(p, dim);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+
+int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  if (!p.scans || !p.counts || !p.pairs || p.n_scans <= 0 || p.n_max <= 0 || p.n_pairs < 0 ||
+      (dim != 2 && dim != 3))
+    return B200ICP_ERR_BAD_ARG;
+  if (p.n_pairs == 0) return B200ICP_OK;
+  if (!workspace || workspace_bytes < 256) return B200ICP_ERR_WORKSPACE;
+  if ((reinterpret_cast<uintptr_t>(p.scans) & 15u) != 0) return B200ICP_ERR_BAD_ARG;
+  const DeviceInfo d = device_info();
+  if (!d.ok) return B200ICP_ERR_NO_DEVICE;
+  p.queue = reinterpret_cast<unsigned int*>(workspace);
+  if (cudaMemsetAsync(workspace, 0, 256, stream) != cudaSuccess) return B200ICP_ERR_CUDA;
+  if (dim == 2 && p.n_max <= kMax2d) {
+    // R sources per thread x W warps: capacity 32*R*W >= n_max, chosen to waste few lanes
+    if (p.n_max <= 256) return launch2d<4, 2, 8>(p, stream, d.sms);
+    if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
+    if (p.n_max <= 1120) return launch2d<7, 5, 4>(p, stream, d.sms);
+    return launch2d<8, 8, 2>(p, stream, d.sms);
+  }
+  return launch3d(p, dim, stream, d.sms);
+}
+
+__global__ void ffma_probe_kernel(float* sink, int iters) {
+  const float a = 1.0f + 1e-7f * threadIdx.x, b = 1e-7f * (blockIdx.x + 1);
+  float x[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) x[k] = (float)k;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int rep = 0; rep < 4; ++rep)
+#pragma unroll
+      for (int k = 0; k < 16; ++k) x[k] = __fmaf_rn(x[k], a, b);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) s += x[k];
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200icp_version(void) { return B200ICP_VERSION; }
+
+const char* b200icp_error_string(int code) {
+  switch (code) {
+    case B200ICP_OK: return "ok";
+    case B200ICP_ERR_BAD_ARG: return "bad argument (null pointer, non-positive size, dim not 2/3, or misaligned scans)";
+    case B200ICP_ERR_TOO_LARGE: return "problem too large for this build";
+    case B200ICP_ERR_WORKSPACE: return "workspace missing or smaller than b200icp_workspace_bytes";
+    case B200ICP_ERR_CUDA: return "CUDA launch failed";
+    case B200ICP_ERR_NO_DEVICE: return "no sm_100 (B200) device is current";
+    default: return "unknown error code";
+  }
+}
+
+int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out) {
+  if (!bytes_out || n_pairs < 0 || n_max <= 0 || (dim != 2 && dim != 3)) return B200ICP_ERR_BAD_ARG;
+  *bytes_out = 256;  // the work-queue counter (padded)
+  return B200ICP_OK;
+}
+
+int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                const int32_t* pairs, const double* init, const double* epsilon,
+                const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!init || !epsilon || !normalize || !T_out || max_iters < 0) return B200ICP_ERR_BAD_ARG;
+  RunParams p{};
+  p.scans = scans; p.counts = counts; p.n_scans = n_scans; p.n_max = n_max;
+  p.pairs = pairs; p.init = init; p.epsilon = epsilon; p.normalize = normalize;
+  p.n_pairs = n_pairs; p.max_iters = max_iters; p.stopping_thresh = stopping_thresh;
+  p.T_out = T_out; p.err_out = err_out; p.iters_out = iters_out; p.status_out = status_out;
+  p.corr_out = corr_out; p.dist2_out = nullptr; p.nearest_only = 0;
+  return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                    const int32_t* pairs, int n_pairs, int32_t* corr_out, double* dist2_out,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  if (!corr_out) return B200ICP_ERR_BAD_ARG;
+  RunParams p{};
+  p.scans = scans; p.counts = counts; p.n_scans = n_scans; p.n_max = n_max;
+  p.pairs = pairs; p.n_pairs = n_pairs; p.max_iters = 0; p.stopping_thresh = 0.0;
+  p.corr_out = corr_out; p.dist2_out = dist2_out; p.nearest_only = 1;
+  return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int b200icp_ffma_probe(float* sink, int n_blocks, int iters, void* stream) {
+  if (!sink || n_blocks <= 0 || iters <= 0) return B200ICP_ERR_BAD_ARG;
+  ffma_probe_kernel<<<n_blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(sink, iters);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+
+}  // extern "C"

@@ -1,0 +1,410 @@
+// Fused planar ICP: one CTA aligns one (source, target) scan pair from staging to
+// the final pose; the whole iterate-until-converged loop stays on the device.
+//
+// Replaces modules/icp.py:123-189 (run_icp) for 2-D scans, i.e. the call shapes
+// of modules/localization.py:120-123 and main.py:162.
+//
+// Per pair:
+//   stage   TMA bulk copies (cp.async.bulk + mbarrier) bring the float64 source
+//           and target scans into shared memory; the target is also kept as
+//           fp32 (x,y) pairs for the search.                      [icp.py:153-161]
+//   pass k  1. q = T_k s in float64, rounded to fp32 for the search [icp.py:116]
+//           2. exhaustive fp32 nearest-neighbour sweep: every thread keeps R
+//              source points in registers, targets are broadcast from shared
+//              memory as LDS.128 (two targets), block minima tracked with
+//              FMNMX3; per 32-target block the best and second-best (value |
+//              block id) are kept.                                  [icp.py:117]
+//           3. exactness: the best block is rescanned, every candidate within a
+//              proven slack of the fp32 minimum is re-evaluated in float64 from
+//              the original coordinates; if a second block is within the slack
+//              the warp rescans all targets cooperatively.  Result == float64
+//              brute force (lowest index on exact ties).
+//           4. float64 sums (centroids, cross-covariance, SSE, bbox), warp
+//              shuffle + one shared-memory exchange.              [icp.py:55-61,88-95]
+//           5. closed-form planar Kabsch (rotation or reflection branch), pose
+//              composition, the reference's three stop tests.  [icp.py:62-72,119,172-181]
+#pragma once
+#include "icp_common.cuh"
+
+namespace b200icp {
+
+constexpr int kSums2d = 9;    // sum qx qy px py qxpx qxpy qypx qypy sse   (shifted by origin)
+constexpr int kRed2d = 17;    // + min/max of qx qy px py
+
+struct Smem2dLayout {
+  int np;          // padded point capacity (multiple of 32)
+  size_t off_t64, off_s64, off_t32, off_red, off_ctl, total;
+};
+__host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps) {
+  Smem2dLayout L;
+  L.np = ((n_max + 31) / 32) * 32;
+  size_t o = 0;
+  L.off_t64 = o; o += (size_t)L.np * 16;
+  L.off_s64 = o; o += (size_t)L.np * 16;
+  L.off_t32 = o; o += (size_t)L.np * 8;
+  L.off_red = o; o += (size_t)2 * warps * kRed2d * 8;
+  L.off_ctl = o; o += 64;
+  L.total = o;
+  return L;
+}
+
+template <int R, int W, int MINB>
+__global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const Smem2dLayout L = smem2d_layout(p.n_max, W);
+  double2* t64 = reinterpret_cast<double2*>(smem_raw + L.off_t64);
+  double2* s64 = reinterpret_cast<double2*>(smem_raw + L.off_s64);
+  float2* t32 = reinterpret_cast<float2*>(smem_raw + L.off_t32);
+  double* red = reinterpret_cast<double*>(smem_raw + L.off_red);
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw + L.off_ctl);
+  int* s_pair = reinterpret_cast<int*>(smem_raw + L.off_ctl + 16);
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int warp = tid >> 5;
+  const int wbase = warp * 32 * R;
+  constexpr float kTruncRel = 1.52587890625e-5f;  // 2^-16 >= the 6 truncated mantissa bits (2^-17)
+  const double kInf = __longlong_as_double(0x7ff0000000000000LL);
+
+  if (tid == 0) {
+    mbar_init(mbar, 1);
+    fence_mbar_init();
+  }
+  uint32_t parity = 0;
+
+  for (;;) {
+    __syncthreads();  // previous pair fully consumed; mbarrier initialised
+    if (tid == 0) *s_pair = (int)atomicAdd(p.queue, 1u);
+    __syncthreads();
+    const int pair = *s_pair;
+    if (pair >= p.n_pairs) break;
+
+    const int si = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
+    int early = -1;
+    int ns = 0, nt = 0;
+    if (si < 0 || ti < 0 || si >= p.n_scans || ti >= p.n_scans) {
+      early = B200ICP_STATUS_SKIPPED;
+    } else {
+      ns = min(p.counts[si], p.n_max);
+      nt = min(p.counts[ti], p.n_max);
+      if (ns <= 0 || nt <= 0) early = B200ICP_STATUS_EMPTY;
+    }
+    // ---- initial transform (planar part) ------------------------------------
+    double r00 = 1, r01 = 0, r10 = 0, r11 = 1, tx = 0, ty = 0, zs = 1;
+    if (early < 0 && !p.nearest_only) {
+      const double* T0 = p.init + (size_t)pair * 16;
+      r00 = T0[0]; r01 = T0[1]; tx = T0[3];
+      r10 = T0[4]; r11 = T0[5]; ty = T0[7];
+      zs = T0[10];
+      const bool planar = T0[2] == 0.0 && T0[6] == 0.0 && T0[8] == 0.0 && T0[9] == 0.0 &&
+                          T0[11] == 0.0 && T0[12] == 0.0 && T0[13] == 0.0 && T0[14] == 0.0 &&
+                          T0[15] == 1.0;
+      if (!planar) early = B200ICP_STATUS_NONPLANAR;
+    }
+    if (early >= 0) {
+      if (tid == 0) {
+        if (p.status_out) p.status_out[pair] = early;
+        if (p.iters_out) p.iters_out[pair] = 0;
+        if (p.err_out) p.err_out[pair] = __longlong_as_double(0x7ff8000000000000LL);
+        if (p.T_out)
+          for (int k = 0; k < 16; ++k) p.T_out[(size_t)pair * 16 + k] = p.init ? p.init[(size_t)pair * 16 + k] : 0.0;
+      }
+      if (p.corr_out)
+        for (int j = tid; j < p.n_max; j += W * 32) p.corr_out[(size_t)pair * p.n_max + j] = -1;
+      continue;
+    }
+
+    // ---- stage both scans with TMA bulk copies --------------------------------
+    if (tid == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(mbar, (uint32_t)(ns + nt) * 16u);
+      tma_load_1d(s64, p.scans + (size_t)si * p.n_max * 2, (uint32_t)ns * 16u, mbar);
+      tma_load_1d(t64, p.scans + (size_t)ti * p.n_max * 2, (uint32_t)nt * 16u, mbar);
+    }
+    mbar_wait(mbar, parity);
+    parity ^= 1u;
+
+    // fp32 copy of the target (+ sentinels), max |coord| and centroid of the target
+    float amax = 0.f;
+    double cx = 0.0, cy = 0.0;
+    for (int i = tid; i < L.np; i += W * 32) {
+      float2 v = make_float2(kBigCoord, kBigCoord);
+      if (i < nt) {
+        double2 t = t64[i];
+        v = make_float2((float)t.x, (float)t.y);
+        amax = fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y)));
+        cx += t.x; cy += t.y;
+      }
+      t32[i] = v;
+    }
+    amax = warp_maxf(amax);
+    cx = warp_sum(cx);
+    cy = warp_sum(cy);
+    if (lane == 0) { red[warp * 3 + 0] = (double)amax; red[warp * 3 + 1] = cx; red[warp * 3 + 2] = cy; }
+    __syncthreads();
+    float tmax = 0.f;
+    double ox = 0.0, oy = 0.0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      tmax = fmaxf(tmax, (float)red[w * 3 + 0]);
+      ox += red[w * 3 + 1]; oy += red[w * 3 + 2];
+    }
+    tmax = tmax * (1.0f + 4.0f * kU);   // fp32 rounding of the inputs
+    ox /= (double)nt; oy /= (double)nt;  // shift origin for the one-pass covariance
+    __syncthreads();                     // red[] is reused by the passes below
+
+    const double epsilon = p.nearest_only ? 0.0 : p.epsilon[pair];
+    const bool normalize = p.nearest_only ? false : (p.normalize[pair] != 0);
+    const int nblk = (nt + kBlockTargets - 1) / kBlockTargets;
+    const bool warp_active = wbase < ns;
+    StopState st{0.0, 0, 0};
+    int passes = 0;
+
+    for (;;) {  // ------------------------------ one ICP pass ------------------------
+      double acc[kRed2d];
+#pragma unroll
+      for (int k = 0; k < kSums2d; ++k) acc[k] = 0.0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { acc[kSums2d + 2 * k] = kInf; acc[kSums2d + 2 * k + 1] = -kInf; }
+      int corr[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) corr[r] = -1;
+
+      if (warp_active) {
+        // 1. transform
+        float qx[R], qy[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int j = wbase + lane + 32 * r;
+          qx[r] = 0.f; qy[r] = 0.f;
+          if (j < ns) {
+            const double2 s = s64[j];
+            qx[r] = (float)fma(r00, s.x, fma(r01, s.y, tx));
+            qy[r] = (float)fma(r10, s.x, fma(r11, s.y, ty));
+          }
+        }
+        // 2. fp32 sweep with per-block (value | block id) top-2 tracking
+        unsigned best[R], second[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) { best[r] = 0xffffffffu; second[r] = 0xffffffffu; }
+        const float4* tv = reinterpret_cast<const float4*>(t32);
+        for (int b = 0; b < nblk; ++b) {
+          float bm[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) bm[r] = __int_as_float(0x7f800000);
+#pragma unroll
+          for (int i = 0; i < kBlockTargets / 2; ++i) {
+            const float4 tt = tv[b * (kBlockTargets / 2) + i];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+              const float d0 = dist2_2d(qx[r], qy[r], tt.x, tt.y);
+              const float d1 = dist2_2d(qx[r], qy[r], tt.z, tt.w);
+              bm[r] = fmin3(bm[r], d0, d1);
+            }
+          }
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const unsigned pk = (__float_as_uint(bm[r]) & 0xffffffc0u) | (unsigned)b;
+            second[r] = min(second[r], max(best[r], pk));
+            best[r] = min(best[r], pk);
+          }
+        }
+        // 3. exact resolution in float64
+        unsigned ambiguous = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int j = wbase + lane + 32 * r;
+          if (j < ns) {
+            const int blk = (int)(best[r] & 63u);
+            const float bval = __uint_as_float(best[r] & 0xffffffc0u);
+            const float sval = __uint_as_float(second[r] & 0xffffffc0u);
+            const float a_bound = fmaxf(fabsf(qx[r]), fabsf(qy[r])) * (1.0f + 4.0f * kU) + tmax;
+            const float thr = candidate_threshold(bval, a_bound, kTruncRel);
+            if (!(sval > thr)) {
+              ambiguous |= 1u << r;
+            } else {
+              unsigned mask = 0;
+              const float2* tb = t32 + blk * kBlockTargets;
+#pragma unroll 8
+              for (int i = 0; i < kBlockTargets; ++i) {
+                const float2 t = tb[i];
+                if (dist2_2d(qx[r], qy[r], t.x, t.y) <= thr) mask |= 1u << i;
+              }
+              const double2 s = s64[j];
+              const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
+              const double qdy = fma(r10, s.x, fma(r11, s.y, ty));
+              double bd = kInf;
+              int bi = -1;
+              while (mask) {
+                const int i = __ffs(mask) - 1;
+                mask &= mask - 1;
+                const int idx = blk * kBlockTargets + i;
+                if (idx < nt) {
+                  const double2 t = t64[idx];
+                  const double ex = qdx - t.x, ey = qdy - t.y;
+                  const double d = ex * ex + ey * ey;
+                  if (d < bd) { bd = d; bi = idx; }
+                }
+              }
+              if (bi < 0) ambiguous |= 1u << r;  // cannot happen for finite data; be safe
+              corr[r] = bi;
+            }
+          }
+        }
+        // 3b. rare: a second block is within the slack -> the warp scans all targets
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          unsigned vote = __ballot_sync(0xffffffffu, (ambiguous >> r) & 1u);
+          while (vote) {
+            const int src_lane = __ffs(vote) - 1;
+            vote &= vote - 1;
+            const float fx = __shfl_sync(0xffffffffu, qx[r], src_lane);
+            const float fy = __shfl_sync(0xffffffffu, qy[r], src_lane);
+            const unsigned bpk = __shfl_sync(0xffffffffu, best[r], src_lane);
+            const float a_bound = fmaxf(fabsf(fx), fabsf(fy)) * (1.0f + 4.0f * kU) + tmax;
+            const float thr = candidate_threshold(__uint_as_float(bpk & 0xffffffc0u), a_bound, kTruncRel);
+            const int j = wbase + src_lane + 32 * r;
+            const double2 s = s64[j];
+            const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
+            const double qdy = fma(r10, s.x, fma(r11, s.y, ty));
+            double bd = kInf;
+            int bi = 0x7fffffff;
+            for (int i = lane; i < nt; i += 32) {
+              const float2 t = t32[i];
+              // !(d > thr) also admits NaN so that non-finite data still yields an index
+              if (!(dist2_2d(fx, fy, t.x, t.y) > thr)) {
+                const double2 td = t64[i];
+                const double ex = qdx - td.x, ey = qdy - td.y;
+                const double d = ex * ex + ey * ey;
+                if (d < bd || bi == 0x7fffffff) { bd = d; bi = i; }
+              }
+            }
+            warp_argmin(bd, bi);
+            if (lane == src_lane) corr[r] = (bi == 0x7fffffff) ? 0 : bi;
+          }
+        }
+        // 4. float64 sums over this thread's matched pairs
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int j = wbase + lane + 32 * r;
+          if (j < ns) {
+            const double2 s = s64[j];
+            const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
+            const double qdy = fma(r10, s.x, fma(r11, s.y, ty));
+            const double2 t = t64[corr[r]];
+            const double ux = qdx - ox, uy = qdy - oy, vx = t.x - ox, vy = t.y - oy;
+            acc[0] += ux; acc[1] += uy; acc[2] += vx; acc[3] += vy;
+            acc[4] = fma(ux, vx, acc[4]); acc[5] = fma(ux, vy, acc[5]);
+            acc[6] = fma(uy, vx, acc[6]); acc[7] = fma(uy, vy, acc[7]);
+            const double ex = qdx - t.x, ey = qdy - t.y;
+            acc[8] += ex * ex + ey * ey;
+            if (normalize) {
+              acc[9] = fmin(acc[9], qdx);   acc[10] = fmax(acc[10], qdx);
+              acc[11] = fmin(acc[11], qdy); acc[12] = fmax(acc[12], qdy);
+              acc[13] = fmin(acc[13], t.x); acc[14] = fmax(acc[14], t.x);
+              acc[15] = fmin(acc[15], t.y); acc[16] = fmax(acc[16], t.y);
+            }
+            if (p.nearest_only && p.dist2_out)
+              p.dist2_out[(size_t)pair * p.n_max + j] = ex * ex + ey * ey;
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kSums2d; ++k) acc[k] = warp_sum(acc[k]);
+        if (normalize) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            acc[kSums2d + 2 * k] = warp_min(acc[kSums2d + 2 * k]);
+            acc[kSums2d + 2 * k + 1] = warp_max(acc[kSums2d + 2 * k + 1]);
+          }
+        }
+      }
+      // exchange: one shared-memory round per pass, double-buffered by pass parity
+      double* slot = red + (size_t)(passes & 1) * W * kRed2d;
+      if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < kRed2d; ++k) slot[warp * kRed2d + k] = acc[k];
+      }
+      __syncthreads();
+      double tot[kRed2d];
+#pragma unroll
+      for (int k = 0; k < kRed2d; ++k) tot[k] = slot[k];
+#pragma unroll
+      for (int w = 1; w < W; ++w) {
+#pragma unroll
+        for (int k = 0; k < kSums2d; ++k) tot[k] += slot[w * kRed2d + k];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          tot[kSums2d + 2 * k] = fmin(tot[kSums2d + 2 * k], slot[w * kRed2d + kSums2d + 2 * k]);
+          tot[kSums2d + 2 * k + 1] = fmax(tot[kSums2d + 2 * k + 1], slot[w * kRed2d + kSums2d + 2 * k + 1]);
+        }
+      }
+      passes += 1;
+
+      // 5. error of this pass (before the update), solve, compose, stop tests
+      double err = tot[8];
+      if (normalize) {
+        const double wx = fmax(tot[10], tot[14]) - fmin(tot[9], tot[13]);
+        const double wy = fmax(tot[12], tot[16]) - fmin(tot[11], tot[15]);
+        const double diag = sqrt(wx * wx + wy * wy);
+        err = err / (diag * diag * (double)ns);
+      }
+      int status;
+      if (p.nearest_only) {
+        status = B200ICP_STATUS_EPSILON;
+      } else {
+        const double inv_n = 1.0 / (double)ns;
+        const double mqx = tot[0] * inv_n, mqy = tot[1] * inv_n;
+        const double mpx = tot[2] * inv_n, mpy = tot[3] * inv_n;
+        const double nn = (double)ns;
+        const double c00 = tot[4] - nn * mqx * mpx, c01 = tot[5] - nn * mqx * mpy;
+        const double c10 = tot[6] - nn * mqy * mpx, c11 = tot[7] - nn * mqy * mpy;
+        double d00, d01, d10, d11, dz;
+        if (c00 * c11 - c01 * c10 >= 0.0) {
+          const double num = c01 - c10, den = c00 + c11;
+          const double h = hypot(num, den);
+          const double co = (h == 0.0) ? 1.0 : den / h, sn = (h == 0.0) ? 0.0 : num / h;
+          d00 = co; d01 = -sn; d10 = sn; d11 = co; dz = 1.0;
+        } else {
+          const double num = c01 + c10, den = c00 - c11;
+          const double h = hypot(num, den);
+          const double co = den / h, sn = num / h;
+          d00 = co; d01 = sn; d10 = sn; d11 = -co; dz = -1.0;
+        }
+        const double qbx = ox + mqx, qby = oy + mqy, pbx = ox + mpx, pby = oy + mpy;
+        const double dtx = pbx - (d00 * qbx + d01 * qby);
+        const double dty = pby - (d10 * qbx + d11 * qby);
+        const double n00 = d00 * r00 + d01 * r10, n01 = d00 * r01 + d01 * r11;
+        const double n10 = d10 * r00 + d11 * r10, n11 = d10 * r01 + d11 * r11;
+        const double ntx = d00 * tx + d01 * ty + dtx, nty = d10 * tx + d11 * ty + dty;
+        r00 = n00; r01 = n01; r10 = n10; r11 = n11; tx = ntx; ty = nty; zs *= dz;
+        status = stop_test(st, err, epsilon, p.max_iters, p.stopping_thresh);
+      }
+      if (status >= 0) {
+        if (tid == 0) {
+          if (p.T_out) {
+            double* T = p.T_out + (size_t)pair * 16;
+            T[0] = r00; T[1] = r01; T[2] = 0.0; T[3] = tx;
+            T[4] = r10; T[5] = r11; T[6] = 0.0; T[7] = ty;
+            T[8] = 0.0; T[9] = 0.0; T[10] = zs; T[11] = 0.0;
+            T[12] = 0.0; T[13] = 0.0; T[14] = 0.0; T[15] = 1.0;
+          }
+          if (p.err_out) p.err_out[pair] = err;
+          if (p.iters_out) p.iters_out[pair] = passes;
+          if (p.status_out) p.status_out[pair] = status;
+        }
+        if (p.corr_out) {
+          int* out = p.corr_out + (size_t)pair * p.n_max;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const int j = wbase + lane + 32 * r;
+            if (j < p.n_max) out[j] = corr[r];
+          }
+          for (int j = W * 32 * R + tid; j < p.n_max; j += W * 32) out[j] = -1;
+        }
+        break;
+      }
+    }
+  }
+}
+
+}  // namespace b200icp

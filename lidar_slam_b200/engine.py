@@ -1,0 +1,229 @@
+"""Host side of the batched ICP engine: device buffers (torch) + the C-ABI calls.
+
+`run_icp_batch` is the new batched entry the reference lacks (its callers loop,
+modules/localization.py:115-130, main.py:161-172, test_icp.py:70-91); per pair
+it has exactly the semantics of the reference's run_icp (modules/icp.py:123-189).
+PyTorch is used for device memory and streams only.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+
+STATUS_NAMES = {
+    0: "epsilon", 1: "max_iters", 2: "stalled", 3: "nonfinite", 4: "empty", 5: "nonplanar_init",
+    6: "skipped",
+}
+STATUS_NONPLANAR = 5
+
+
+@dataclass
+class IcpBatchResult:
+    """Per-pair results, all on the device the inputs live on."""
+    T: torch.Tensor          # [B,4,4] float64, transforms[-1] of icp.py:183-189
+    error: torch.Tensor      # [B] float64, error of the last executed pass
+    iters: torch.Tensor      # [B] int32, executed passes
+    status: torch.Tensor     # [B] int32, see STATUS_NAMES
+    corr: Optional[torch.Tensor]  # [B,n_max] int32 or None
+
+
+def _device():
+    if not torch.cuda.is_available():
+        raise RuntimeError("lidar_slam_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream_ptr():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _to_dev(x, dtype, dev):
+    if isinstance(x, torch.Tensor):
+        return x.to(device=dev, dtype=dtype).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype).to(dev)
+
+
+def pack_scans(clouds: Sequence[np.ndarray], device=None):
+    """Ragged list of (n_i, D) arrays -> padded pool [S, n_max, D] float64 + counts [S] int32.
+
+    This is the layout of the scan pool in HBM: one row of n_max*D float64 per scan,
+    valid points first.  n_max is rounded up to an even count so that every row
+    starts 16-byte aligned for the TMA bulk copies.
+    """
+    device = device or _device()
+    if len(clouds) == 0:
+        raise ValueError("no point clouds given")
+    dim = int(np.asarray(clouds[0]).shape[1])
+    if dim not in (2, 3):
+        raise ValueError("point clouds must have shape (N,2) or (N,3)")
+    n_max = max(int(np.asarray(c).shape[0]) for c in clouds)
+    if n_max == 0:
+        raise ValueError("empty point cloud")
+    n_max += n_max & 1
+    pool = np.zeros((len(clouds), n_max, dim), dtype=np.float64)
+    counts = np.zeros((len(clouds),), dtype=np.int32)
+    for i, c in enumerate(clouds):
+        c = np.asarray(c, dtype=np.float64)
+        if c.ndim != 2 or c.shape[1] != dim:
+            raise ValueError("all point clouds of a pool must share their dimension")
+        pool[i, :c.shape[0]] = c
+        counts[i] = c.shape[0]
+    return torch.from_numpy(pool).to(device), torch.from_numpy(counts).to(device)
+
+
+def _per_pair(x, n, dtype, dev):
+    if isinstance(x, (int, float, bool, np.floating, np.integer, np.bool_)):
+        return torch.full((n,), x, dtype=dtype, device=dev)
+    t = _to_dev(x, dtype, dev).reshape(-1)
+    if t.numel() != n:
+        raise ValueError("per-pair parameter has the wrong length")
+    return t
+
+
+def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_iters=2000,
+                  stopping_thresh=0.0001, normalize_error=False, return_correspondences=False,
+                  planar_fallback=True) -> IcpBatchResult:
+    """Align every (source, target) pair of `pairs` in one launch.
+
+    scans  [S, n_max, D] float64 (D = 2 or 3), counts [S] int32 (see pack_scans);
+    pairs  [B, 2] int32 rows (source scan, target scan);
+    init_transforms [B,4,4] float64 (default identity);
+    epsilon, normalize_error: scalar or length-B (so that odometry pairs and
+    loop-closure pairs with different settings share one launch);
+    max_iters, stopping_thresh: scalars, as modules/icp.py:128-129.
+    """
+    lib = _lib.load()
+    dev = scans.device if isinstance(scans, torch.Tensor) and scans.is_cuda else _device()
+    scans = _to_dev(scans, torch.float64, dev)
+    if scans.dim() != 3 or scans.shape[2] not in (2, 3):
+        raise ValueError("scans must have shape [S, n_max, 2|3]")
+    n_scans, n_max, dim = scans.shape
+    if (n_max * dim) % 2:
+        raise ValueError("n_max*dim must be even (16-byte aligned rows); use pack_scans")
+    counts = _to_dev(counts, torch.int32, dev)
+    pairs = _to_dev(pairs, torch.int32, dev).reshape(-1, 2)
+    n_pairs = pairs.shape[0]
+    if init_transforms is None:
+        init = torch.eye(4, dtype=torch.float64, device=dev).repeat(n_pairs, 1, 1)
+    else:
+        init = _to_dev(init_transforms, torch.float64, dev).reshape(-1, 4, 4)
+        if init.shape[0] != n_pairs:
+            raise ValueError("init_transforms must have one 4x4 per pair")
+    eps = _per_pair(epsilon, n_pairs, torch.float64, dev)
+    norm = _per_pair(normalize_error, n_pairs, torch.uint8, dev)
+
+    T = torch.empty((n_pairs, 4, 4), dtype=torch.float64, device=dev)
+    err = torch.empty((n_pairs,), dtype=torch.float64, device=dev)
+    iters = torch.empty((n_pairs,), dtype=torch.int32, device=dev)
+    status = torch.empty((n_pairs,), dtype=torch.int32, device=dev)
+    corr = torch.empty((n_pairs, n_max), dtype=torch.int32, device=dev) if return_correspondences else None
+    if n_pairs == 0:
+        return IcpBatchResult(T, err, iters, status, corr)
+
+    nbytes = ctypes.c_size_t()
+    _lib.check(lib.b200icp_workspace_bytes(n_pairs, n_max, dim, ctypes.byref(nbytes)), "b200icp_workspace_bytes")
+    ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
+
+    def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax):
+        with torch.cuda.device(dev):
+            _lib.check(lib.b200icp_run(
+                _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
+                _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
+                _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
+                _stream_ptr()), "b200icp_run")
+
+    launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
+
+    if dim == 2 and planar_fallback:
+        # The planar kernel refuses initial transforms that leave the plane (status 5); the
+        # reference would lift the scan to z = 0 and carry on in 3-D (icp.py:153-156), so
+        # those pairs are re-run through the general kernel on a z-padded copy.
+        bad = torch.nonzero(status == STATUS_NONPLANAR).reshape(-1)
+        if bad.numel() > 0:
+            scans3 = torch.zeros((n_scans, n_max, 3), dtype=torch.float64, device=dev)
+            scans3[:, :, :2] = scans
+            sub = lambda t: None if t is None else t[bad].contiguous()
+            T2, e2, i2, s2 = sub(T), sub(err), sub(iters), sub(status)
+            c2 = sub(corr)
+            launch(3, scans3, sub(pairs), sub(init), sub(eps), sub(norm), T2, e2, i2, s2, c2, n_max)
+            T[bad], err[bad], iters[bad], status[bad] = T2, e2, i2, s2
+            if corr is not None:
+                corr[bad] = c2
+    return IcpBatchResult(T, err, iters, status, corr)
+
+
+def nearest_batch(scans, counts, pairs, return_dist2=False):
+    """Exact nearest neighbour of every point of scan pairs[b,0] in scan pairs[b,1]
+    (get_correspondences / KDTree.query, modules/icp.py:29-41), no transform."""
+    lib = _lib.load()
+    dev = scans.device if isinstance(scans, torch.Tensor) and scans.is_cuda else _device()
+    scans = _to_dev(scans, torch.float64, dev)
+    n_scans, n_max, dim = scans.shape
+    counts = _to_dev(counts, torch.int32, dev)
+    pairs = _to_dev(pairs, torch.int32, dev).reshape(-1, 2)
+    n_pairs = pairs.shape[0]
+    corr = torch.empty((n_pairs, n_max), dtype=torch.int32, device=dev)
+    d2 = torch.empty((n_pairs, n_max), dtype=torch.float64, device=dev) if return_dist2 else None
+    nbytes = ctypes.c_size_t()
+    _lib.check(lib.b200icp_workspace_bytes(n_pairs, n_max, dim, ctypes.byref(nbytes)), "b200icp_workspace_bytes")
+    ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.b200icp_nearest(_ptr(scans), _ptr(counts), n_scans, n_max, dim, _ptr(pairs), n_pairs,
+                                       _ptr(corr), _ptr(d2), _ptr(ws), ws.numel(), _stream_ptr()),
+                   "b200icp_nearest")
+    return (corr, d2) if return_dist2 else corr
+
+
+def voxel_downsample_device(points: torch.Tensor, voxel_size: float) -> torch.Tensor:
+    """Device voxel_downsample (modules/icp.py:4-27) on an [N,3] float64 CUDA tensor."""
+    lib = _lib.load()
+    dev = points.device
+    points = points.to(torch.float64).contiguous()
+    n = points.shape[0]
+    nbytes = ctypes.c_size_t()
+    with torch.cuda.device(dev):
+        _lib.check(lib.b200icp_voxel_workspace_bytes(n, ctypes.byref(nbytes)), "b200icp_voxel_workspace_bytes")
+        ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
+        out = torch.empty((n, 3), dtype=torch.float64, device=dev)
+        n_out = torch.zeros((1,), dtype=torch.int32, device=dev)
+        _lib.check(lib.b200icp_voxel_downsample(_ptr(points), n, float(voxel_size), _ptr(out), _ptr(n_out),
+                                                _ptr(ws), ws.numel(), _stream_ptr()), "b200icp_voxel_downsample")
+    m = int(n_out.item())
+    if m < 0:
+        raise ValueError("voxel grid exceeds 2^21 cells along an axis; use a larger voxel_size")
+    return out[:m]
+
+
+def ffma_peak_tflops(seconds: float = 0.3) -> dict:
+    """Measured FP32 FFMA issue rate of the current device (the NN kernel's roofline
+    denominator): lane-FFMA/s and the equivalent TFLOP/s (2 flops per FFMA)."""
+    lib = _lib.load()
+    dev = _device()
+    props = torch.cuda.get_device_properties(dev)
+    blocks = props.multi_processor_count * 8
+    sink = torch.empty((blocks * 256,), dtype=torch.float32, device=dev)
+    iters = 4096
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 0.0
+    for rep in range(6):
+        start.record()
+        _lib.check(lib.b200icp_ffma_probe(_ptr(sink), blocks, iters, _stream_ptr()), "b200icp_ffma_probe")
+        stop.record()
+        stop.synchronize()
+        ms = start.elapsed_time(stop)
+        rate = blocks * 256 * iters * 64 / (ms * 1e-3)
+        if rep > 0:
+            best = max(best, rate)
+        if ms < seconds * 1e3 / 8 and rep == 0:
+            iters *= max(1, int(seconds * 1e3 / 8 / max(ms, 1e-3)))
+    return {"lane_ffma_per_s": best, "tflops": 2 * best / 1e12, "sms": props.multi_processor_count}
