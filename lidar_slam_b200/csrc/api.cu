@@ -1,5 +1,6 @@
 // extern "C" entry points of libb200icp.so (see include/b200icp.h).
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "icp2d.cuh"
 #include "icp3d.cuh"
@@ -64,10 +65,16 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
   p.queue = reinterpret_cast<unsigned int*>(workspace);
   if (cudaMemsetAsync(workspace, 0, 256, stream) != cudaSuccess) return B200ICP_ERR_CUDA;
   if (dim == 2 && p.n_max <= kMax2d) {
-    // R sources per thread x W warps: capacity 32*R*W >= n_max, chosen to waste few lanes
-    if (p.n_max <= 256) return launch2d<4, 2, 8>(p, stream, d.sms);
+    // W warps, up to R rows of 32 source points per warp: capacity 32*R*W >= n_max
+    if (p.n_max <= 256) return launch2d<2, 4, 8>(p, stream, d.sms);
     if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
-    if (p.n_max <= 1120) return launch2d<7, 5, 4>(p, stream, d.sms);
+    if (p.n_max <= 1280) {
+      const char* v = getenv("B200ICP_VARIANT");
+      if (v && v[0] == 'a') return launch2d<10, 4, 4>(p, stream, d.sms);
+      if (v && v[0] == 'b') return launch2d<5, 8, 4>(p, stream, d.sms);
+      if (v && v[0] == 'c') return launch2d<3, 16, 2>(p, stream, d.sms);
+      return launch2d<5, 8, 3>(p, stream, d.sms);
+    }
     return launch2d<8, 8, 2>(p, stream, d.sms);
   }
   return launch3d(p, dim, stream, d.sms);

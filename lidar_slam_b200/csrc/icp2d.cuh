@@ -48,13 +48,61 @@ __host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps) {
   return L;
 }
 
+// Shared-memory layout of the fp32 target copy: groups of four targets stored as
+// [x0 x1 x2 x3 y0 y1 y2 y3], so one LDS.128 yields two (x,x) register pairs ready for the
+// packed fp32x2 instructions.
+__device__ __forceinline__ float2 target32(const float* t32, int i) {
+  const float* g = t32 + (i >> 2) * 8 + (i & 3);
+  return make_float2(g[0], g[4]);
+}
+
+// The NN sweep for NR source points per thread (rows of 32 sources per warp).
+// Per 4 candidates: 2x(FADD2, FADD2, FMUL2, FFMA2) + 2 FMNMX3, i.e. 8 FP32-pipe issue slots
+// carrying the 16 algorithmic lane-instructions, plus 0.5 ALU slot per candidate.
+template <int NR, int RMAX>
+__device__ __forceinline__ void sweep2d(const float* t32, int nblk, const float (&qx)[RMAX],
+                                        const float (&qy)[RMAX], unsigned (&best)[RMAX],
+                                        unsigned (&second)[RMAX]) {
+  f32x2 qxx[NR], qyy[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) { qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); }
+  const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(t32);
+  for (int b = 0; b < nblk; ++b) {
+    float bm[NR];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) bm[r] = __int_as_float(0x7f800000);
+#pragma unroll
+    for (int i = 0; i < kBlockTargets / 4; ++i) {
+      const ulonglong2 X = tp[b * (kBlockTargets / 2) + 2 * i];
+      const ulonglong2 Y = tp[b * (kBlockTargets / 2) + 2 * i + 1];
+#pragma unroll
+      for (int r = 0; r < NR; ++r) {
+        f32x2 dx = sub2(qxx[r], X.x), dy = sub2(qyy[r], Y.x);
+        const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
+        dx = sub2(qxx[r], X.y); dy = sub2(qyy[r], Y.y);
+        const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
+        float d0, d1, d2, d3;
+        unpack2(d01, d0, d1);
+        unpack2(d23, d2, d3);
+        bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const unsigned pk = (__float_as_uint(bm[r]) & 0xffffffc0u) | (unsigned)b;
+      second[r] = min(second[r], max(best[r], pk));
+      best[r] = min(best[r], pk);
+    }
+  }
+}
+
 template <int R, int W, int MINB>
 __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const Smem2dLayout L = smem2d_layout(p.n_max, W);
   double2* t64 = reinterpret_cast<double2*>(smem_raw + L.off_t64);
   double2* s64 = reinterpret_cast<double2*>(smem_raw + L.off_s64);
-  float2* t32 = reinterpret_cast<float2*>(smem_raw + L.off_t32);
+  float* t32 = reinterpret_cast<float*>(smem_raw + L.off_t32);
   double* red = reinterpret_cast<double*>(smem_raw + L.off_red);
   uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw + L.off_ctl);
   int* s_pair = reinterpret_cast<int*>(smem_raw + L.off_ctl + 16);
@@ -62,7 +110,6 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
   const int tid = threadIdx.x;
   const int lane = tid & 31;
   const int warp = tid >> 5;
-  const int wbase = warp * 32 * R;
   constexpr float kTruncRel = 1.52587890625e-5f;  // 2^-16 >= the 6 truncated mantissa bits (2^-17)
   const double kInf = __longlong_as_double(0x7ff0000000000000LL);
 
@@ -135,7 +182,8 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         amax = fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y)));
         cx += t.x; cy += t.y;
       }
-      t32[i] = v;
+      float* g = t32 + (i >> 2) * 8 + (i & 3);
+      g[0] = v.x; g[4] = v.y;
     }
     amax = warp_maxf(amax);
     cx = warp_sum(cx);
@@ -156,7 +204,12 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     const double epsilon = p.nearest_only ? 0.0 : p.epsilon[pair];
     const bool normalize = p.nearest_only ? false : (p.normalize[pair] != 0);
     const int nblk = (nt + kBlockTargets - 1) / kBlockTargets;
-    const bool warp_active = wbase < ns;
+    // rows of 32 source points are dealt out evenly: warp w owns rows [row0, row0 + nr)
+    const int rows = (ns + 31) >> 5;
+    const int nr = rows / W + (warp < rows % W ? 1 : 0);
+    const int row0 = warp * (rows / W) + min(warp, rows % W);
+    const int wbase = row0 * 32;
+    const bool warp_active = nr > 0;
     StopState st{0.0, 0, 0};
     int passes = 0;
 
@@ -177,7 +230,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         for (int r = 0; r < R; ++r) {
           const int j = wbase + lane + 32 * r;
           qx[r] = 0.f; qy[r] = 0.f;
-          if (j < ns) {
+          if (r < nr && j < ns) {
             const double2 s = s64[j];
             qx[r] = (float)fma(r00, s.x, fma(r01, s.y, tx));
             qy[r] = (float)fma(r10, s.x, fma(r11, s.y, ty));
@@ -187,34 +240,23 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         unsigned best[R], second[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) { best[r] = 0xffffffffu; second[r] = 0xffffffffu; }
-        const float4* tv = reinterpret_cast<const float4*>(t32);
-        for (int b = 0; b < nblk; ++b) {
-          float bm[R];
-#pragma unroll
-          for (int r = 0; r < R; ++r) bm[r] = __int_as_float(0x7f800000);
-#pragma unroll
-          for (int i = 0; i < kBlockTargets / 2; ++i) {
-            const float4 tt = tv[b * (kBlockTargets / 2) + i];
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-              const float d0 = dist2_2d(qx[r], qy[r], tt.x, tt.y);
-              const float d1 = dist2_2d(qx[r], qy[r], tt.z, tt.w);
-              bm[r] = fmin3(bm[r], d0, d1);
-            }
-          }
-#pragma unroll
-          for (int r = 0; r < R; ++r) {
-            const unsigned pk = (__float_as_uint(bm[r]) & 0xffffffc0u) | (unsigned)b;
-            second[r] = min(second[r], max(best[r], pk));
-            best[r] = min(best[r], pk);
-          }
+        switch (nr) {
+#define B200ICP_SWEEP_CASE(N) \
+  case N:                     \
+    if constexpr (N <= R) sweep2d<N, R>(t32, nblk, qx, qy, best, second); \
+    break;
+          B200ICP_SWEEP_CASE(1) B200ICP_SWEEP_CASE(2) B200ICP_SWEEP_CASE(3) B200ICP_SWEEP_CASE(4)
+          B200ICP_SWEEP_CASE(5) B200ICP_SWEEP_CASE(6) B200ICP_SWEEP_CASE(7) B200ICP_SWEEP_CASE(8)
+          B200ICP_SWEEP_CASE(9) B200ICP_SWEEP_CASE(10) B200ICP_SWEEP_CASE(11) B200ICP_SWEEP_CASE(12)
+#undef B200ICP_SWEEP_CASE
+          default: break;
         }
         // 3. exact resolution in float64
         unsigned ambiguous = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const int j = wbase + lane + 32 * r;
-          if (j < ns) {
+          if (r < nr && j < ns) {
             const int blk = (int)(best[r] & 63u);
             const float bval = __uint_as_float(best[r] & 0xffffffc0u);
             const float sval = __uint_as_float(second[r] & 0xffffffc0u);
@@ -224,11 +266,14 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
               ambiguous |= 1u << r;
             } else {
               unsigned mask = 0;
-              const float2* tb = t32 + blk * kBlockTargets;
-#pragma unroll 8
-              for (int i = 0; i < kBlockTargets; ++i) {
-                const float2 t = tb[i];
-                if (dist2_2d(qx[r], qy[r], t.x, t.y) <= thr) mask |= 1u << i;
+              const float4* tb = reinterpret_cast<const float4*>(t32 + blk * (2 * kBlockTargets));
+#pragma unroll 2
+              for (int g = 0; g < kBlockTargets / 4; ++g) {
+                const float4 X = tb[2 * g], Y = tb[2 * g + 1];
+                if (dist2_2d(qx[r], qy[r], X.x, Y.x) <= thr) mask |= 1u << (4 * g);
+                if (dist2_2d(qx[r], qy[r], X.y, Y.y) <= thr) mask |= 2u << (4 * g);
+                if (dist2_2d(qx[r], qy[r], X.z, Y.z) <= thr) mask |= 4u << (4 * g);
+                if (dist2_2d(qx[r], qy[r], X.w, Y.w) <= thr) mask |= 8u << (4 * g);
               }
               const double2 s = s64[j];
               const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
@@ -270,7 +315,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
             double bd = kInf;
             int bi = 0x7fffffff;
             for (int i = lane; i < nt; i += 32) {
-              const float2 t = t32[i];
+              const float2 t = target32(t32, i);
               // !(d > thr) also admits NaN so that non-finite data still yields an index
               if (!(dist2_2d(fx, fy, t.x, t.y) > thr)) {
                 const double2 td = t64[i];
@@ -287,7 +332,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const int j = wbase + lane + 32 * r;
-          if (j < ns) {
+          if (r < nr && j < ns) {
             const double2 s = s64[j];
             const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
             const double qdy = fma(r10, s.x, fma(r11, s.y, ty));
@@ -397,9 +442,9 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 #pragma unroll
           for (int r = 0; r < R; ++r) {
             const int j = wbase + lane + 32 * r;
-            if (j < p.n_max) out[j] = corr[r];
+            if (r < nr && j < ns) out[j] = corr[r];
           }
-          for (int j = W * 32 * R + tid; j < p.n_max; j += W * 32) out[j] = -1;
+          for (int j = ns + tid; j < p.n_max; j += W * 32) out[j] = -1;
         }
         break;
       }

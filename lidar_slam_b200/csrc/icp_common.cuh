@@ -29,6 +29,34 @@ __device__ __forceinline__ float dist2_3d(float qx, float qy, float qz, float tx
   return __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, __fmul_rn(dz, dz)));
 }
 
+// Packed fp32x2 arithmetic (Blackwell FADD2 / FMUL2 / FFMA2): two IEEE round-to-nearest
+// operations per lane per issue slot, bit-identical to the scalar intrinsics above, so the
+// sweep (packed, two targets at a time) and the rescans (scalar) agree exactly.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
 // Three-input fp32 minimum: one FMNMX3 on sm_100 (PTX ISA 8.6+).
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
   float r;

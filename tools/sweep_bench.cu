@@ -1,0 +1,224 @@
+// Developer microbenchmark: throughput ceiling of NN-sweep inner-loop variants on B200.
+// nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o tools/sweep_bench tools/sweep_bench.cu
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+#include <vector>
+
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+  float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
+}
+__device__ __forceinline__ float dist2(float qx, float qy, float tx, float ty) {
+  float dx = __fsub_rn(qx, tx), dy = __fsub_rn(qy, ty);
+  return __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+}
+
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void up2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+// VAR 5: direct form with packed f32x2 math over target pairs (SoA x4/y4 layout) + FMNMX3 + top2
+// VAR 0: direct form + FMNMX3 + top-2 bookkeeping per 32 (as in icp2d.cuh)
+// VAR 1: direct form + two FMNMX + bookkeeping
+// VAR 2: direct form + FMNMX3, no bookkeeping (pure min)
+// VAR 3: expanded form (2 FFMA, t2 in smem as float4 {x,y,t2,pad}) + FMNMX3 + bookkeeping
+// VAR 4: direct form, FMNMX3 over 4 candidates via two ops but with SoA float4 x4,y4 loads (4 targets/2 LDS)
+template <int R, int W, int MINB, int VAR>
+__global__ void __launch_bounds__(W * 32, MINB) sweep(const float* tg, int nt, int iters, float* out) {
+  extern __shared__ __align__(16) float sm[];
+  const int np = ((nt + 31) / 32) * 32;
+  for (int i = threadIdx.x; i < np * 4; i += W * 32) sm[i] = 0.f;
+  __syncthreads();
+  if (VAR == 3) {
+    for (int i = threadIdx.x; i < np; i += W * 32) {
+      float x = i < nt ? tg[2 * i] : 1e18f, y = i < nt ? tg[2 * i + 1] : 1e18f;
+      sm[4 * i] = x; sm[4 * i + 1] = y; sm[4 * i + 2] = x * x + y * y; sm[4 * i + 3] = 0.f;
+    }
+  } else if (VAR == 4 || VAR == 5) {
+    for (int i = threadIdx.x; i < np; i += W * 32) {
+      float x = i < nt ? tg[2 * i] : 1e18f, y = i < nt ? tg[2 * i + 1] : 1e18f;
+      sm[(i / 4) * 8 + (i % 4)] = x; sm[(i / 4) * 8 + 4 + (i % 4)] = y;
+    }
+  } else {
+    for (int i = threadIdx.x; i < np; i += W * 32) {
+      sm[2 * i] = i < nt ? tg[2 * i] : 1e18f; sm[2 * i + 1] = i < nt ? tg[2 * i + 1] : 1e18f;
+    }
+  }
+  __syncthreads();
+  float qx[R], qy[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    int j = (blockIdx.x * W * 32 + threadIdx.x) * R + r;
+    qx[r] = tg[2 * (j % nt)] + 0.01f; qy[r] = tg[2 * (j % nt) + 1] - 0.01f;
+  }
+  unsigned accb = 0, accs = 0;
+  const int nblk = np / 32;
+  const float4* tv = reinterpret_cast<const float4*>(sm);
+  for (int it = 0; it < iters; ++it) {
+    unsigned best[R], second[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) { best[r] = 0xffffffffu; second[r] = 0xffffffffu; }
+    for (int b = 0; b < nblk; ++b) {
+      float bm[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) bm[r] = __int_as_float(0x7f800000);
+      if (VAR == 3) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float4 t = tv[b * 32 + i];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            float s = __fmaf_rn(qx[r], t.x, __fmaf_rn(qy[r], t.y, t.z));
+            if (i & 1) bm[r] = fmin3(bm[r], s, second[r] == 7u ? 0.f : s); else bm[r] = fminf(bm[r], s);
+          }
+        }
+      } else if (VAR == 5) {
+        const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(sm);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const ulonglong2 X = tp[b * 16 + 2 * i], Y = tp[b * 16 + 2 * i + 1];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const u64 qxx = pk2(qx[r], qx[r]), qyy = pk2(qy[r], qy[r]);
+            u64 dx = sub2(qxx, X.x), dy = sub2(qyy, Y.x);
+            u64 d01 = fma2(dx, dx, mul2(dy, dy));
+            dx = sub2(qxx, X.y); dy = sub2(qyy, Y.y);
+            u64 d23 = fma2(dx, dx, mul2(dy, dy));
+            float d0, d1, d2, d3; up2(d01, d0, d1); up2(d23, d2, d3);
+            bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
+          }
+        }
+      } else if (VAR == 4) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 X = tv[b * 16 + 2 * i], Y = tv[b * 16 + 2 * i + 1];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            float d0 = dist2(qx[r], qy[r], X.x, Y.x), d1 = dist2(qx[r], qy[r], X.y, Y.y);
+            float d2 = dist2(qx[r], qy[r], X.z, Y.z), d3 = dist2(qx[r], qy[r], X.w, Y.w);
+            bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 tt = tv[b * 16 + i];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const float d0 = dist2(qx[r], qy[r], tt.x, tt.y), d1 = dist2(qx[r], qy[r], tt.z, tt.w);
+            if (VAR == 1) bm[r] = fminf(fminf(bm[r], d0), d1); else bm[r] = fmin3(bm[r], d0, d1);
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        if (VAR == 2) {
+          best[r] = min(best[r], __float_as_uint(bm[r]));
+        } else {
+          const unsigned pk = (__float_as_uint(bm[r]) & 0xffffffc0u) | (unsigned)b;
+          second[r] = min(second[r], max(best[r], pk));
+          best[r] = min(best[r], pk);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) { accb ^= best[r]; accs += second[r]; qx[r] += 1e-4f; qy[r] -= 1e-4f; }
+  }
+  out[blockIdx.x * W * 32 + threadIdx.x] = __uint_as_float(accb) + (float)accs;
+}
+
+__global__ void ffma2_probe(float* sink, int iters) {
+  const u64 a = pk2(1.0f + 1e-7f * threadIdx.x, 1.0f), b = pk2(1e-7f * (blockIdx.x + 1), 1e-7f);
+  u64 x[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) x[k] = pk2((float)k, (float)k + 0.5f);
+  for (int it = 0; it < iters; ++it)
+#pragma unroll
+    for (int rep = 0; rep < 4; ++rep)
+#pragma unroll
+      for (int k = 0; k < 16; ++k) x[k] = fma2(x[k], a, b);
+  float s = 0.f;
+  for (int k = 0; k < 16; ++k) { float lo, hi; up2(x[k], lo, hi); s += lo + hi; }
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void ffma_probe(float* sink, int iters) {
+  const float a = 1.0f + 1e-7f * threadIdx.x, b = 1e-7f * (blockIdx.x + 1);
+  float x[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) x[k] = (float)k;
+  for (int it = 0; it < iters; ++it)
+#pragma unroll
+    for (int rep = 0; rep < 4; ++rep)
+#pragma unroll
+      for (int k = 0; k < 16; ++k) x[k] = __fmaf_rn(x[k], a, b);
+  float s = 0.f;
+  for (int k = 0; k < 16; ++k) s += x[k];
+  sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+static float* d_t; static float* d_out; static double g_peak;
+
+template <int R, int W, int MINB, int VAR>
+void run(const char* name, int nt, int iters) {
+  auto k = sweep<R, W, MINB, VAR>;
+  size_t smem = (size_t)((nt + 31) / 32) * 32 * 16;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int per = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k, W * 32, smem);
+  int grid = per * 148;
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    cudaEventRecord(e0); k<<<grid, W * 32, smem>>>(d_t, nt, iters, d_out); cudaEventRecord(e1);
+    cudaEventSynchronize(e1); float ms; cudaEventElapsedTime(&ms, e0, e1); if (rep && ms < best) best = ms;
+  }
+  double cand = (double)grid * W * 32 * R * (double)(((nt + 31) / 32) * 32) * iters;
+  double rate = cand * 4 / (best * 1e-3);
+  printf("%-34s R=%d W=%d cta/sm=%d  %.3f ms  cand/s %.3e  4*cand/s %.3e  frac_of_ffma_probe %.3f  err=%s\n", name, R, W, per,
+         best, cand / (best * 1e-3), rate, rate / g_peak, cudaGetErrorString(cudaGetLastError()));
+}
+
+int main() {
+  const int nt = 1081;
+  std::vector<float> h(2 * nt);
+  for (int i = 0; i < nt; ++i) { float a = -2.356f + 4.712f * i / 1080.f; float r = 3.f + 2.f * sinf(5 * a); h[2 * i] = r * cosf(a); h[2 * i + 1] = r * sinf(a); }
+  cudaMalloc(&d_t, h.size() * 4); cudaMemcpy(d_t, h.data(), h.size() * 4, cudaMemcpyHostToDevice);
+  cudaMalloc(&d_out, 148 * 32 * 1024 * 4);
+  {
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+      cudaEventRecord(e0); ffma_probe<<<148 * 8, 256>>>(d_out, 20000); cudaEventRecord(e1); cudaEventSynchronize(e1);
+      float ms; cudaEventElapsedTime(&ms, e0, e1); if (rep && ms < best) best = ms;
+    }
+    g_peak = 148.0 * 8 * 256 * 20000 * 64 / (best * 1e-3);
+    printf("ffma probe: %.3e lane-FFMA/s\n", g_peak);
+    best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+      cudaEventRecord(e0); ffma2_probe<<<148 * 8, 256>>>(d_out, 20000); cudaEventRecord(e1); cudaEventSynchronize(e1);
+      float ms; cudaEventElapsedTime(&ms, e0, e1); if (rep && ms < best) best = ms;
+    }
+    printf("ffma2 probe: %.3e lane-FMA/s (2 per lane per instr)\n", 2 * 148.0 * 8 * 256 * 20000 * 64 / (best * 1e-3));
+  }
+  const int it = 40;
+  run<9, 4, 4, 0>("direct+min3+top2", nt, it);
+  run<9, 4, 5, 0>("direct+min3+top2 (5cta)", nt, it);
+  run<7, 4, 6, 0>("direct+min3+top2", nt, it);
+  run<8, 4, 4, 0>("direct+min3+top2", nt, it);
+  run<12, 4, 3, 0>("direct+min3+top2", nt, it);
+  run<9, 8, 2, 0>("direct+min3+top2", nt, it);
+  run<9, 4, 4, 1>("direct+2xFMNMX+top2", nt, it);
+  run<9, 4, 4, 2>("direct+min3 only", nt, it);
+  run<9, 4, 4, 4>("direct SoA x4 + min3 + top2", nt, it);
+  run<9, 4, 4, 5>("direct f32x2 + min3 + top2", nt, it);
+  run<5, 8, 3, 5>("direct f32x2 + min3 + top2", nt, it);
+  run<6, 4, 6, 5>("direct f32x2 + min3 + top2", nt, it);
+  run<5, 8, 3, 0>("direct+min3+top2", nt, it);
+  run<5, 8, 3, 4>("direct SoA x4 + min3 + top2", nt, it);
+  run<3, 16, 2, 0>("direct+min3+top2", nt, it);
+  run<9, 4, 4, 3>("expanded 2xFFMA", nt, it);
+  run<12, 4, 4, 3>("expanded 2xFFMA", nt, it);
+  run<16, 4, 3, 3>("expanded 2xFFMA", nt, it);
+  return 0;
+}
