@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""Benchmark of the ICP hot path (BASELINE.json metric: ICP scan-pair alignments/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of the hot path over one batch: config 2 of BASELINE.json,
+`main.py --mode scan_matching --dataset 20` -> 4955 consecutive 1081-beam 2-D scan pairs
+(synthetic scans) per GPU; with N > 1 every rank aligns its own
+4955-pair shard (weak scaling) and ONE all-gather returns all relative poses to every rank.
+
+Printed JSON (one line, rank 0): see the keys at the bottom.  `value` is measured with the
+inputs resident in HBM; `e2e` goes through the public host-facing API with pinned HOST
+buffers, H2D and D2H copies inside the timed region.  `roofline` is the fused ICP kernel
+against the FP32 CUDA-core issue rate measured live by the library's FFMA probe;
+`cpu_baseline` is the oracle port of the reference (scipy KD-tree + LAPACK SVD) on the
+host cores.  `--impl reference` times that CPU implementation alone.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+PAIRS_PER_GPU = 4955          # config 2: dataset 20 has 4956 synced scans -> 4955 pairs
+N_POOLS = 2                   # distinct scan pools rotated between steps (2 x 85.7 MB > 126 MB L2)
+EPSILON, MAX_ITERS, STOP = 1e-3, 2000, 1e-4   # localization.py:120-123 + icp.py defaults
+METRIC = "icp_scan_pair_alignments_per_sec"
+UNIT = "pairs/s"
+
+
+# --------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference, all host cores (used by cpu_baseline and
+# by --impl reference).  This is the ONLY place bench.py touches oracle/.
+# --------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    path, lo, hi = args
+    os.environ["OPENBLAS_NUM_THREADS"] = "1"
+    os.environ["OMP_NUM_THREADS"] = "1"
+    from oracle import icp_oracle as orc
+    scans = np.load(os.path.join(path, "scans.npy"), mmap_mode="r")     # shared page cache
+    counts = np.load(os.path.join(path, "counts.npy"))
+    pairs = np.load(os.path.join(path, "pairs.npy"))
+    init = np.load(os.path.join(path, "init.npy"))
+    t0 = time.perf_counter()
+    passes = 0
+    for k in range(lo, hi):
+        s, t = pairs[k]
+        _, _, _, n = orc.run_icp_info(np.asarray(scans[s, :counts[s]]), np.asarray(scans[t, :counts[t]]),
+                                      init[k], epsilon=EPSILON, max_iters=MAX_ITERS, stopping_thresh=STOP)
+        passes += n
+    return time.perf_counter() - t0, passes
+
+
+class CpuReference:
+    """The CPU port on `cores` persistent worker processes (one per core).  `sample(seed)`
+    stages the first n_sample pairs of the workload with that seed; `run(seed)` times one
+    pass over them: contiguous shards, wall time of the slowest worker."""
+
+    def __init__(self, n_sample, cores=None):
+        import multiprocessing as mp
+        cores = cores or os.cpu_count() or 1
+        self.cores = max(1, min(cores, n_sample))
+        self.n_sample = n_sample
+        self.dirs = {}
+        bounds = np.linspace(0, n_sample, self.cores + 1).astype(int)
+        self.shards = [(int(bounds[i]), int(bounds[i + 1])) for i in range(self.cores) if bounds[i + 1] > bounds[i]]
+        self.pool = mp.get_context("spawn").Pool(len(self.shards))
+
+    def sample(self, seed):
+        from lidar_slam_b200 import synth
+        if seed not in self.dirs:
+            b = synth.odometry_batch(self.n_sample, seed=seed, device="cpu", n_traj=1)
+            path = tempfile.mkdtemp(prefix="b200icp_cpu_")
+            for name in ("scans", "counts", "pairs", "init"):
+                np.save(os.path.join(path, name + ".npy"), b[name].numpy())
+            self.dirs[seed] = path
+        return self.dirs[seed]
+
+    def run(self, seed):
+        path = self.sample(seed)
+        out = self.pool.map(_cpu_worker, [(path, lo, hi) for lo, hi in self.shards], chunksize=1)
+        slowest = max(t for t, _ in out)
+        return {"value": self.n_sample / slowest, "cores": len(self.shards), "pairs": self.n_sample,
+                "seconds": slowest, "mean_passes": sum(p for _, p in out) / self.n_sample}
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+        for path in self.dirs.values():
+            for name in ("scans", "counts", "pairs", "init"):
+                os.remove(os.path.join(path, name + ".npy"))
+            os.rmdir(path)
+
+
+def _cpu_sample_size():
+    cores = os.cpu_count() or 1
+    return int(min(PAIRS_PER_GPU, max(512, 96 * cores)))
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n_sample = _cpu_sample_size()
+    if args.steps * n_sample > 40 * 4955:          # keep the whole run within a few minutes
+        n_sample = max(256, 40 * 4955 // args.steps)
+    ref = CpuReference(n_sample)
+    ref.run(seed=20)                                # warm-up: imports, page cache, KD-tree code paths
+    vals, secs = [], 0.0
+    for k in range(args.steps):
+        r = ref.run(seed=20 + 10 * (k % N_POOLS))
+        vals.append(r)
+        secs += r["seconds"]
+    ref.close()
+    value = sum(r["pairs"] for r in vals) / secs
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "config2: 4955 consecutive 1081-beam 2-D scan pairs (main.py --mode scan_matching "
+                               "--dataset 20 shape)",
+                   "epsilon": EPSILON, "max_iters": MAX_ITERS, "stopping_thresh": STOP,
+                   "sample": f"first {n_sample} pairs of each step's pool"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": vals[0]["cores"], "kind": "port",
+                         "sample": f"{n_sample} pairs per step x {args.steps} steps, oracle port of modules/icp.py "
+                                   f"(scipy KDTree + numpy SVD), one process per core, slowest worker",
+                         "mean_passes": vals[0]["mean_passes"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
+                "samples": len(rows), "power_w_max": max(float(r[2]) for r in rows)}
+
+
+# --------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    from lidar_slam_b200 import engine, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    B = args.pairs
+    # ---- workload: N_POOLS distinct config-2 shaped batches per rank, generated on the device ----
+    pools = []
+    for k in range(N_POOLS):
+        b = synth.odometry_batch(B, seed=20 + 10 * k + 1000 * rank, device=dev, n_traj=1)
+        pools.append({n: b[n].contiguous() for n in ("scans", "counts", "pairs", "init")})
+    host = []
+    for pl in pools:      # pinned host copies for the end-to-end leg
+        host.append({n: t.cpu().pin_memory() for n, t in pl.items()})
+    h2d_bytes = sum(t.numel() * t.element_size() for t in host[0].values())
+    gathered = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
+    host_out = torch.empty((world * B, 4), dtype=torch.float64).pin_memory()
+    d2h_bytes = host_out.numel() * host_out.element_size()
+
+    def step_device(k):
+        pl = pools[k % N_POOLS]
+        res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
+                                   max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False)
+        poses = engine.pack_poses(res.T, res.error)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, poses)
+        else:
+            gathered.copy_(poses)
+        return res
+
+    def step_e2e(k):
+        hp = host[k % N_POOLS]          # HOST buffers in, HOST poses out, every step
+        res = engine.run_icp_batch(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
+                                   max_iters=MAX_ITERS, stopping_thresh=STOP)
+        poses = engine.pack_poses(res.T, res.error)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, poses)
+            host_out.copy_(gathered, non_blocking=True)
+        else:
+            host_out.copy_(poses, non_blocking=True)
+        torch.cuda.synchronize()        # the caller reads the poses
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- FP32 issue-rate probe (roofline denominator), before the timed regions ----
+    peak = engine.ffma_peak_tflops()
+
+    # ---- warm-up ----
+    results = {}
+    for k in range(max(args.warmup, N_POOLS)):
+        results[k % N_POOLS] = step_device(k)
+    barrier()
+
+    # per-step work (identical every time a pool is reused): candidate distance evaluations
+    cand = []
+    for k in range(N_POOLS):
+        pl, res = pools[k], results[k]
+        cn = pl["counts"].double()
+        pr = pl["pairs"].long()
+        cand.append(float((res.iters.double() * cn[pr[:, 0]] * cn[pr[:, 1]]).sum().item()))
+    mean_passes = float(sum(r.iters.double().mean().item() for r in results.values()) / N_POOLS)
+    ok = all(bool(((r.status == 0) | (r.status == 2)).all().item()) for r in results.values())
+
+    # ---- timed region 1: inputs resident in HBM ----
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    ev0.record()
+    for k in range(args.steps):
+        step_device(k)
+    ev1.record()
+    barrier()
+    t_wall1 = time.perf_counter()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+
+    # ---- the dominant kernel alone (CUDA events on the launching stream) ----
+    barrier()
+    kernel_ms, kernel_cand = 0.0, 0.0
+    for k in range(args.steps):
+        pl = pools[k % N_POOLS]
+        kev[k][0].record()
+        engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
+                             max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False)
+        kev[k][1].record()
+    torch.cuda.synchronize()
+    for k in range(args.steps):
+        kernel_ms += kev[k][0].elapsed_time(kev[k][1])
+        kernel_cand += cand[k % N_POOLS]
+    clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
+
+    # ---- timed region 2: end to end through the host-facing API ----
+    for k in range(2):
+        step_e2e(k)
+    barrier()
+    ev0.record()
+    for k in range(args.steps):
+        step_e2e(k)
+    ev1.record()
+    barrier()
+    ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    value = world * B * args.steps / (ms_total * 1e-3)
+    e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
+    lane_instr_per_s = 4.0 * kernel_cand / (kernel_ms * 1e-3)          # 4 FP32-pipe lane-instructions / candidate
+    sms = peak["sms"]
+    nominal = sms * 128 * 1.965e9
+    bytes_per_pair = 2 * 1081 * 16 + 128 + 32                          # two fp64 scans + init + result
+    roofline = {
+        "bound": "fp32_cuda_core_issue",
+        "kernel": "b200icp::icp2d_kernel (fused ICP: NN sweep + exact resolve + Kabsch + stop tests)",
+        "achieved": lane_instr_per_s * 1.25 / 1e12, "peak": peak["lane_ffma_per_s"] * 2 / 1e12, "unit": "TFLOP/s",
+        "frac": lane_instr_per_s / peak["lane_ffma_per_s"],
+        "frac_note": "instruction-issue fraction: 4 algorithmic FP32 lane-instructions (5 flops) per candidate "
+                     "distance / measured FFMA lane-instructions per second (b200icp_ffma_probe, this run); "
+                     "achieved/peak in TFLOP/s are shown at 5 flops per candidate vs 2 flops per FFMA, so "
+                     "achieved/peak = 0.625 * frac",
+        "achieved_lane_instr_per_s": lane_instr_per_s, "peak_lane_instr_per_s": peak["lane_ffma_per_s"],
+        "peak_source": "measured live: b200icp_ffma_probe (MEASURED_PEAKS.json has no FP32 CUDA-core figure)",
+        "frac_of_nominal_1965mhz": lane_instr_per_s / nominal,
+        "kernel_ms_per_launch": kernel_ms / args.steps,
+        "pair_iterations_per_s": kernel_cand / (1081.0 * 1081.0) / (kernel_ms * 1e-3),
+        "hbm_algorithmic_gbs": bytes_per_pair * B * args.steps / (kernel_ms * 1e-3) / 1e9,
+        "hbm_peak_gbs": _measured_hbm(), "traffic": None,
+    }
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, N_POOLS), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32 search + f64 solve", "data": "synthetic",
+        "config": {"workload": "config2: 4955 consecutive 1081-beam 2-D scan pairs per GPU "
+                               "(main.py --mode scan_matching --dataset 20 shape)",
+                   "pairs_per_gpu": B, "points_per_scan": "1081 beams, ~1075 valid", "epsilon": EPSILON,
+                   "max_iters": MAX_ITERS, "stopping_thresh": STOP, "mean_passes_per_pair": mean_passes,
+                   "l2": f"{N_POOLS} distinct scan pools of 85.7 MB rotated between steps (171 MB > 126 MB L2)",
+                   "exchange": "one NCCL all_gather_into_tensor of [B,4] f64 per step" if world > 1 else "none (1 GPU)",
+                   "all_pairs_converged": ok},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": 2 * args.steps,     # icp2d_kernel + pack_poses_kernel per step
+        "roofline": roofline,
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        n_sample = min(B, _cpu_sample_size())
+        ref = CpuReference(n_sample)
+        ref.run(seed=20)
+        r = ref.run(seed=20)
+        ref.close()
+        line["cpu_baseline"] = {
+            "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+            "sample": f"first {n_sample} pairs of pool 0, oracle port of modules/icp.py (scipy KDTree + numpy "
+                      f"SVD), one process per core, slowest worker {r['seconds']:.1f} s",
+            "mean_passes": r["mean_passes"]}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def _measured_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f).get("hbm_gbs")
+    except OSError:
+        return 6650.0   # B200_PROFILING.md fallback
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step (default: config 2)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

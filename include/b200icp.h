@@ -100,6 +100,13 @@ int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int
                     const int32_t* pairs, int n_pairs, int32_t* corr_out, double* dist2_out,
                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* Pack results for the multi-GPU exchange: out[b] = (x, y, theta, error) with
+ * x, y = T[0][3], T[1][3] and theta = atan2(T[1][0], T[0][0]), i.e. pose_from_T of
+ * modules/utils.py:196-210 applied to TSE2_from_TSE3(T) (utils.py:212-225), which is what
+ * the pose-graph builder consumes (main.py:152-155,163-171).  T [n,4,4], err [n],
+ * out [n,4] float64. */
+int b200icp_pack_poses(const double* T, const double* err, int n, double* out, void* stream);
+
 /* FP32 FFMA issue-rate probe used as the roofline denominator: launches a
  * register-only FFMA loop on every SM.  Performs `iters` * 64 dependent-free
  * FFMAs per thread on a grid of n_blocks x 256 threads; the caller times it with

@@ -23,6 +23,7 @@ SIGNATURES = {
                             c_void_p, c_void_p, c_size_t, c_void_p]),
     "b200icp_nearest": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200icp_pack_poses": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "b200icp_ffma_probe": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "b200icp_voxel_workspace_bytes": (c_int, [c_int, ctypes.POINTER(c_size_t)]),
     "b200icp_voxel_downsample": (c_int, [c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p,

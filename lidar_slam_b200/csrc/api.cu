@@ -97,6 +97,18 @@ __global__ void ffma_probe_kernel(float* sink, int iters) {
   sink[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+__global__ void pack_poses_kernel(const double* T, const double* err, int n, double* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* t = T + (size_t)i * 16;
+  double4 o;
+  o.x = t[3];
+  o.y = t[7];
+  o.z = atan2(t[4], t[0]);
+  o.w = err ? err[i] : 0.0;
+  reinterpret_cast<double4*>(out)[i] = o;
+}
+
 }  // namespace
 
 extern "C" {
@@ -145,6 +157,13 @@ int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int
   p.pairs = pairs; p.n_pairs = n_pairs; p.max_iters = 0; p.stopping_thresh = 0.0;
   p.corr_out = corr_out; p.dist2_out = dist2_out; p.nearest_only = 1;
   return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int b200icp_pack_poses(const double* T, const double* err, int n, double* out, void* stream) {
+  if (!T || !out || n < 0) return B200ICP_ERR_BAD_ARG;
+  if (n == 0) return B200ICP_OK;
+  pack_poses_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(T, err, n, out);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
 }
 
 int b200icp_ffma_probe(float* sink, int n_blocks, int iters, void* stream) {

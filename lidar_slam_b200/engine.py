@@ -48,9 +48,17 @@ def _stream_ptr():
 
 
 def _to_dev(x, dtype, dev):
+    """Host arrays / tensors -> contiguous device tensor (async when the source is pinned)."""
     if isinstance(x, torch.Tensor):
-        return x.to(device=dev, dtype=dtype).contiguous()
+        return x.to(device=dev, dtype=dtype, non_blocking=True).contiguous()
     return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype).to(dev)
+
+
+def _keeps_plane(init: torch.Tensor) -> bool:
+    """True if every 4x4 maps the z = 0 plane to itself with a unit homogeneous row, i.e. has the
+    form TSE3_from_TSE2 produces (modules/utils.py:227-240)."""
+    zero = init[:, [0, 1, 2, 2, 2, 3, 3, 3], [2, 2, 0, 1, 3, 0, 1, 2]]
+    return bool(((zero == 0).all() & (init[:, 3, 3] == 1).all()).item())
 
 
 def pack_scans(clouds: Sequence[np.ndarray], device=None):
@@ -113,9 +121,17 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     counts = _to_dev(counts, torch.int32, dev)
     pairs = _to_dev(pairs, torch.int32, dev).reshape(-1, 2)
     n_pairs = pairs.shape[0]
+    planar_ok = True
     if init_transforms is None:
         init = torch.eye(4, dtype=torch.float64, device=dev).repeat(n_pairs, 1, 1)
     else:
+        if dim == 2 and planar_fallback and n_pairs > 0:
+            # checked where the transforms already live: free for host inputs, one small device
+            # reduction (and a sync) for device inputs -- pass planar_fallback=False to skip it
+            # when the caller guarantees TSE3_from_TSE2-shaped inits (status 5 flags violations).
+            host = init_transforms if isinstance(init_transforms, torch.Tensor) else \
+                torch.as_tensor(np.asarray(init_transforms, dtype=np.float64))
+            planar_ok = _keeps_plane(host.reshape(-1, 4, 4))
         init = _to_dev(init_transforms, torch.float64, dev).reshape(-1, 4, 4)
         if init.shape[0] != n_pairs:
             raise ValueError("init_transforms must have one 4x4 per pair")
@@ -142,24 +158,66 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
                 _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
                 _stream_ptr()), "b200icp_run")
 
-    launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
-
-    if dim == 2 and planar_fallback:
-        # The planar kernel refuses initial transforms that leave the plane (status 5); the
-        # reference would lift the scan to z = 0 and carry on in 3-D (icp.py:153-156), so
-        # those pairs are re-run through the general kernel on a z-padded copy.
-        bad = torch.nonzero(status == STATUS_NONPLANAR).reshape(-1)
-        if bad.numel() > 0:
-            scans3 = torch.zeros((n_scans, n_max, 3), dtype=torch.float64, device=dev)
-            scans3[:, :, :2] = scans
-            sub = lambda t: None if t is None else t[bad].contiguous()
-            T2, e2, i2, s2 = sub(T), sub(err), sub(iters), sub(status)
-            c2 = sub(corr)
-            launch(3, scans3, sub(pairs), sub(init), sub(eps), sub(norm), T2, e2, i2, s2, c2, n_max)
-            T[bad], err[bad], iters[bad], status[bad] = T2, e2, i2, s2
-            if corr is not None:
-                corr[bad] = c2
+    if dim == 2 and planar_fallback and not planar_ok:
+        # An initial transform that leaves the plane: the reference lifts the scans to z = 0 and
+        # carries on in 3-D (icp.py:153-156), so the whole batch goes through the general kernel
+        # on a z-padded copy of the pool.
+        scans3 = torch.zeros((n_scans, n_max, 3), dtype=torch.float64, device=dev)
+        scans3[:, :, :2] = scans
+        launch(3, scans3, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
+    else:
+        launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
     return IcpBatchResult(T, err, iters, status, corr)
+
+
+def pack_poses(T: torch.Tensor, error: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[B,4,4] transforms (+ errors) -> [B,4] float64 rows (x, y, theta, error): pose_from_T of
+    modules/utils.py:196-210; the payload of the multi-GPU all-gather."""
+    lib = _lib.load()
+    T = T.contiguous()
+    out = torch.empty((T.shape[0], 4), dtype=torch.float64, device=T.device)
+    with torch.cuda.device(T.device):
+        _lib.check(lib.b200icp_pack_poses(_ptr(T), _ptr(error), T.shape[0], _ptr(out), _stream_ptr()),
+                   "b200icp_pack_poses")
+    return out
+
+
+def shard_range(n_items: int, rank: int, world: int):
+    """Contiguous block partition used for pairs: rank r owns [lo, hi); every rank gets
+    ceil(n/world) slots so that the all-gather is uniform (tail slots are padding)."""
+    per = -(-n_items // world)
+    lo = min(rank * per, n_items)
+    return lo, min(lo + per, n_items), per
+
+
+def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, **kw):
+    """Multi-GPU entry: every rank holds the scan pool (or at least the scans its pairs use),
+    aligns its contiguous shard of `pairs`, and ONE all-gather (NCCL over NVLink on GPUs, gloo
+    in the CPU tests of the host logic) returns [B,4] (x, y, theta, error) rows for all pairs,
+    in pair order, on every rank -- what the pose-graph builder needs (main.py:148-172).
+    Pairs are independent, so there is no other exchange.
+    """
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    pairs_t = pairs if isinstance(pairs, torch.Tensor) else torch.as_tensor(np.asarray(pairs))
+    pairs_t = pairs_t.reshape(-1, 2)
+    n = pairs_t.shape[0]
+    lo, hi, per = shard_range(n, rank, world)
+    init_loc = None if init_transforms is None else init_transforms[lo:hi]
+    for key in ("epsilon", "normalize_error"):
+        v = kw.get(key)
+        if v is not None and not isinstance(v, (int, float, bool)):
+            kw[key] = v[lo:hi]
+    res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, **kw)
+    local = torch.full((per, 4), float("nan"), dtype=torch.float64, device=res.T.device)
+    if hi > lo:
+        local[:hi - lo] = pack_poses(res.T, res.error)
+    if world == 1:
+        return local[:n], res
+    gathered = torch.empty((world * per, 4), dtype=torch.float64, device=local.device)
+    dist.all_gather_into_tensor(gathered, local, group=group)
+    return gathered[:n], res
 
 
 def nearest_batch(scans, counts, pairs, return_dist2=False):
