@@ -106,7 +106,7 @@ class CpuReference:
 
 def _cpu_sample_size():
     cores = os.cpu_count() or 1
-    return int(min(PAIRS_PER_GPU, max(512, 96 * cores)))
+    return int(min(PAIRS_PER_GPU, max(512, 256 * cores)))
 
 
 def run_reference_arm(args):
