@@ -69,10 +69,6 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (p.n_max <= 256) return launch2d<2, 4, 8>(p, stream, d.sms);
     if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
     if (p.n_max <= 1280) {
-      const char* v = getenv("B200ICP_VARIANT");
-      if (v && v[0] == 'a') return launch2d<10, 4, 4>(p, stream, d.sms);
-      if (v && v[0] == 'b') return launch2d<5, 8, 4>(p, stream, d.sms);
-      if (v && v[0] == 'c') return launch2d<3, 16, 2>(p, stream, d.sms);
       return launch2d<5, 8, 3>(p, stream, d.sms);
     }
     return launch2d<8, 8, 2>(p, stream, d.sms);

@@ -367,7 +367,11 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       double* slot = red + (size_t)(passes & 1) * W * kRed2d;
       if (lane == 0) {
 #pragma unroll
-        for (int k = 0; k < kRed2d; ++k) slot[warp * kRed2d + k] = acc[k];
+        for (int k = 0; k < kSums2d; ++k) slot[warp * kRed2d + k] = acc[k];
+        if (normalize) {
+#pragma unroll
+          for (int k = kSums2d; k < kRed2d; ++k) slot[warp * kRed2d + k] = acc[k];
+        }
       }
       __syncthreads();
       double tot[kRed2d];
@@ -377,10 +381,15 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       for (int w = 1; w < W; ++w) {
 #pragma unroll
         for (int k = 0; k < kSums2d; ++k) tot[k] += slot[w * kRed2d + k];
+      }
+      if (normalize) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          tot[kSums2d + 2 * k] = fmin(tot[kSums2d + 2 * k], slot[w * kRed2d + kSums2d + 2 * k]);
-          tot[kSums2d + 2 * k + 1] = fmax(tot[kSums2d + 2 * k + 1], slot[w * kRed2d + kSums2d + 2 * k + 1]);
+        for (int w = 1; w < W; ++w) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            tot[kSums2d + 2 * k] = fmin(tot[kSums2d + 2 * k], slot[w * kRed2d + kSums2d + 2 * k]);
+            tot[kSums2d + 2 * k + 1] = fmax(tot[kSums2d + 2 * k + 1], slot[w * kRed2d + kSums2d + 2 * k + 1]);
+          }
         }
       }
       passes += 1;
