@@ -124,6 +124,32 @@ int b200icp_voxel_downsample(const double* points, int n_points, double voxel_si
                              int32_t* n_out, void* workspace, size_t workspace_bytes,
                              void* stream);
 
+/* ---- scan construction (the producer of the scan pool) ---------------------------------
+ * Replaces get_lidar_data (modules/localization.py:252-307): for every scan, beams with
+ * range_min <= r <= range_max are kept in beam order (localization.py:288-290), converted
+ * x = r*cos(a) + off_x, y = r*sin(a) + off_y (localization.py:293-301; the reference's lidar
+ * offset is off_x = 0.13323, off_y = 0) and written as the leading points of row `scan` of the
+ * padded pool b200icp_run reads.  cos_tab / sin_tab [n_beams] are cos / sin of
+ * linspace(-135 deg, +135 deg, n_beams) (localization.py:273-278) evaluated by the caller, so
+ * that the result is bit-identical to numpy's.  ranges [n_scans, n_beams] float64;
+ * scans_out [n_scans, n_max, 2] float64 (n_max even, rows zero-filled past the count);
+ * counts_out [n_scans] int32. */
+int b200icp_scans_from_ranges(const double* ranges, int n_scans, int n_beams, const double* cos_tab,
+                              const double* sin_tab, double range_min, double range_max,
+                              double off_x, double off_y, double* scans_out, int32_t* counts_out,
+                              int n_max, void* stream);
+
+/* Replaces statistical_outliers_removal (modules/localization.py:223-250) on the pool, in
+ * place: d = sqrt(x^2 + y^2) of every valid point of every scan, threshold = mean(d) +
+ * k_std * std(d) (population std, as np.std), then every scan keeps, in order, its points
+ * with d < threshold; counts are updated and freed slots zeroed.  stats_out [4] device
+ * float64 receives {mean, std, threshold, n_points}.  The two global sums are reduced in a
+ * fixed (deterministic) order that differs from numpy's pairwise order, so mean/std agree
+ * with the reference to a few ulp; a point within that of the threshold may differ. */
+int b200icp_range_filter_workspace_bytes(size_t* bytes_out);
+int b200icp_range_filter(double* scans, int32_t* counts, int n_scans, int n_max, double k_std,
+                         double* stats_out, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

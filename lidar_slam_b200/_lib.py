@@ -28,6 +28,11 @@ SIGNATURES = {
     "b200icp_voxel_workspace_bytes": (c_int, [c_int, ctypes.POINTER(c_size_t)]),
     "b200icp_voxel_downsample": (c_int, [c_void_p, c_int, c_double, c_void_p, c_void_p, c_void_p,
                                          c_size_t, c_void_p]),
+    "b200icp_scans_from_ranges": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_double, c_double,
+                                          c_double, c_double, c_void_p, c_void_p, c_int, c_void_p]),
+    "b200icp_range_filter_workspace_bytes": (c_int, [ctypes.POINTER(c_size_t)]),
+    "b200icp_range_filter": (c_int, [c_void_p, c_void_p, c_int, c_int, c_double, c_void_p, c_void_p,
+                                     c_size_t, c_void_p]),
 }
 
 _lib = None
