@@ -150,6 +150,37 @@ int b200icp_range_filter_workspace_bytes(size_t* bytes_out);
 int b200icp_range_filter(double* scans, int32_t* counts, int n_scans, int n_max, double k_std,
                          double* stats_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- occupancy-grid mapping (the consumer of the poses) ----------------------------------
+ * Replaces OccupancyGridMap.build_map / update_map / bresenham2D / world2grid
+ * (modules/ogm.py:46-60, :149-195, :197-231, :104-126) for n_maps maps built side by side from
+ * the same scans and n_maps pose sequences.  Per scan s and ray i: end point to the world
+ * frame with the pose's rotation (ogm.py:160-162), start cell = world2grid(pose + (0.13323, 0))
+ * (ogm.py:165-169; the reference does not rotate the offset), Bresenham line, every in-bounds
+ * cell but the last gets  cell = f32(f64(cell) - log 4),  the last in-bounds cell
+ * cell = f32(f64(cell) + log 4)  (ogm.py:172-188), in ray order; after each scan the grid is
+ * clipped to [-20, 20] (ogm.py:191).  Results are bit-identical to the reference's float32 grid
+ * (the per-cell update order is reproduced), except that the end-point rotation uses separate
+ * rounded multiply/adds where numpy's BLAS may fuse them: an end point within 1 ulp of a cell
+ * border can land in the neighbouring cell.
+ *
+ * log_odds [n_maps, width, height] float32, row-major, updated in place (zero it for a new map).
+ * poses    [n_maps, n_scans, 3] float64 (x, y, yaw);  cos_sin [n_maps, n_scans, 2] float64 =
+ *          (cos yaw, sin yaw) evaluated by the caller (bit-identical to numpy's).
+ * scans / counts: the scan pool of b200icp_run with dim == 2 (robot-frame end points).
+ * n_max <= 32767.  Workspace from b200icp_ogm_workspace_bytes. */
+int b200icp_ogm_workspace_bytes(int width, int height, int n_max, int n_maps, size_t* bytes_out);
+int b200icp_ogm_build(float* log_odds, int width, int height, double res, double min_x, double min_y,
+                      const double* poses, const double* cos_sin, const double* scans,
+                      const int32_t* counts, int n_scans, int n_max, int n_maps, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* The thresholding at the end of build_map (ogm.py:62-65): grid = 1 where
+ * 1/(1+exp(log_odds)) > 0.5, else 0.  The float32 comparison is monotone in log_odds, so the
+ * caller passes the largest float32 log-odds value that the reference maps to 1
+ * (`one_at_or_below`, found once on the host with the reference's own float32 expression). */
+int b200icp_ogm_binarize(const float* log_odds, uint8_t* grid, long long n_cells, float one_at_or_below,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -33,6 +33,10 @@ SIGNATURES = {
     "b200icp_range_filter_workspace_bytes": (c_int, [ctypes.POINTER(c_size_t)]),
     "b200icp_range_filter": (c_int, [c_void_p, c_void_p, c_int, c_int, c_double, c_void_p, c_void_p,
                                      c_size_t, c_void_p]),
+    "b200icp_ogm_workspace_bytes": (c_int, [c_int, c_int, c_int, c_int, ctypes.POINTER(c_size_t)]),
+    "b200icp_ogm_build": (c_int, [c_void_p, c_int, c_int, c_double, c_double, c_double, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
+    "b200icp_ogm_binarize": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, ctypes.c_float, c_void_p]),
 }
 
 _lib = None
