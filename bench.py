@@ -342,7 +342,9 @@ def run_b200_arm(args):
         "kernel_ms_per_launch": kernel_ms / args.steps,
         "pair_iterations_per_s": kernel_cand / (1081.0 * 1081.0) / (kernel_ms * 1e-3),
         "hbm_algorithmic_gbs": bytes_per_pair * B * args.steps / (kernel_ms * 1e-3) / 1e9,
-        "hbm_peak_gbs": _measured_hbm(), "traffic": None,
+        "hbm_peak_gbs": _measured_hbm(), "traffic": _ncu_traffic(),
+        "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, one ncu --set full capture of this command; profiles/)",
+        "algorithmic_bytes_per_launch": bytes_per_pair * B,
     }
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -376,6 +378,19 @@ def run_b200_arm(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def _ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (or None)."""
+    import glob
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*icp2d_traffic.json"))):
+        try:
+            with open(path) as f:
+                best = json.load(f)["dram_bytes_per_launch"]
+        except (OSError, ValueError, KeyError):
+            pass
+    return best
 
 
 def _measured_hbm():
