@@ -181,6 +181,36 @@ int b200icp_ogm_build(float* log_odds, int width, int height, double res, double
 int b200icp_ogm_binarize(const float* log_odds, uint8_t* grid, long long n_cells, float one_at_or_below,
                          void* stream);
 
+/* ---- texture mapping (RGB-D splat onto the grid) -----------------------------------------
+ * Replaces the frame loop of generate_texture_map (modules/texture_mapping.py:49-96) with its
+ * helpers get_depth_image (:132-143), get_rgbi_rgbj (:145-160), vectorized_generate_point_cloud
+ * (:162-224) and transform_point_cloud (:226-240): every pixel of every frame is turned into a
+ * depth (float32 chain), an RGB look-up position and an optical-frame point (float64), carried
+ * optical -> camera -> robot -> world, mapped to a cell with world2grid (ogm.py:118-119) and,
+ * if inside the grid, painted.  The reference paints frames in order and pixels in row-major
+ * order with last-writer-wins; the kernel folds (frame, pixel, colour) into one 64-bit key per
+ * cell with atomicMax, which yields the same winner without ordering the work.
+ *
+ * keys        [width*height] uint64 device state, zero = unpainted; successive calls with
+ *             increasing frame_base accumulate (frame_base + n_frames < 2^20 - 1).
+ * disparity   [n_frames, img_h, img_w] float32;  rgb [n_frames, img_h, img_w, 3] uint8 (RGB).
+ * T_wr        [n_frames, 16] float64 (device) row-major world <- robot (texture_mapping.py:71-81, built
+ *             by the caller with numpy's cos/sin); K_inv [9] = inv(K); T_cam_from_optical [16] =
+ *             inv(T_oc) (:213-222); T_robot_from_cam [16] = T_rc -- these three are HOST pointers (small
+ *             constants copied into the launch).  img_h*img_w < 2^20.
+ * Products and sums are rounded one by one; numpy's BLAS may fuse them, so a point within an
+ * ulp of a cell border can land in the neighbouring cell. */
+int b200icp_texture_paint(unsigned long long* keys, int width, int height, double res, double min_x,
+                          double min_y, const float* disparity, const uint8_t* rgb, int n_frames,
+                          int img_h, int img_w, int frame_base, const double* T_wr,
+                          const double* K_inv, const double* T_cam_from_optical,
+                          const double* T_robot_from_cam, void* stream);
+
+/* texture_out [width, height, 3] float32 = (painted colour, else the grid_map value on all three
+ * channels (texture_mapping.py:46-47; grid may be NULL = 0)) / 255 (:98). */
+int b200icp_texture_resolve(const unsigned long long* keys, const uint8_t* grid, float* texture_out,
+                            int width, int height, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

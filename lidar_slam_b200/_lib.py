@@ -37,6 +37,10 @@ SIGNATURES = {
     "b200icp_ogm_build": (c_int, [c_void_p, c_int, c_int, c_double, c_double, c_double, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b200icp_ogm_binarize": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, ctypes.c_float, c_void_p]),
+    "b200icp_texture_paint": (c_int, [c_void_p, c_int, c_int, c_double, c_double, c_double, c_void_p, c_void_p,
+                                      c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p]),
+    "b200icp_texture_resolve": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
 }
 
 _lib = None
