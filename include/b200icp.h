@@ -163,7 +163,9 @@ int b200icp_range_filter(double* scans, int32_t* counts, int n_scans, int n_max,
  * rounded multiply/adds where numpy's BLAS may fuse them: an end point within 1 ulp of a cell
  * border can land in the neighbouring cell.
  *
- * log_odds [n_maps, width, height] float32, row-major, updated in place (zero it for a new map).
+ * log_odds [n_maps, width, height] float32, row-major, updated in place (zero it for a new map;
+ *          values must lie in [-20, 20] on entry, which the clip guarantees for any map built by
+ *          this entry or by the reference).
  * poses    [n_maps, n_scans, 3] float64 (x, y, yaw);  cos_sin [n_maps, n_scans, 2] float64 =
  *          (cos yaw, sin yaw) evaluated by the caller (bit-identical to numpy's).
  * scans / counts: the scan pool of b200icp_run with dim == 2 (robot-frame end points).
