@@ -1,0 +1,86 @@
+"""GPU parity at BASELINE.json's full sizes through size-independent properties plus sampled
+oracle checks: config 2 (4955 consecutive 1081-beam pairs), a config-5 shard (65 536 pairs
+generated on the device) and batch-position invariance."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import icp_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_sample(b, res, idx, eps):
+    scans, counts = b["scans"], b["counts"]
+    pairs, init = b["pairs"].cpu().numpy(), b["init"]
+    for k in idx:
+        s, t = pairs[k]
+        src = scans[s, :counts[s]].cpu().numpy()
+        tgt = scans[t, :counts[t]].cpu().numpy()
+        T, err, corr, passes = orc.run_icp_info(src, tgt, init[k].cpu().numpy(), epsilon=eps)
+        assert int(res.iters[k]) == passes, (k, int(res.iters[k]), passes)
+        assert np.abs(res.T[k].cpu().numpy() - T).max() < 1e-9            # north_star asks 1e-5 m / rad
+        assert abs(float(res.error[k]) - err) <= 1e-9 * max(abs(err), 1e-30)
+        if res.corr is not None:
+            assert np.array_equal(res.corr[k, :counts[s]].cpu().numpy(), corr)
+
+
+def test_config2_full_batch_properties_and_sampled_oracle():
+    import lidar_slam_b200 as eng
+    from lidar_slam_b200 import synth
+    b = synth.odometry_batch(4955, seed=20, device="cuda")
+    res = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3,
+                            return_correspondences=True)
+    st = res.status.cpu().numpy()
+    assert set(np.unique(st)) <= {0, 2}                                   # epsilon or stalled, never max_iters / nonfinite
+    assert int(res.iters.min()) >= 1 and int(res.iters.max()) < 2000
+    # every correspondence is a valid target index, -1 beyond the source count
+    cnt = b["counts"].long()
+    src_n = cnt[b["pairs"][:, 0].long()]
+    tgt_n = cnt[b["pairs"][:, 1].long()]
+    col = torch.arange(res.corr.shape[1], device="cuda")[None, :]
+    valid = col < src_n[:, None]
+    assert bool(((res.corr >= 0) & (res.corr < tgt_n[:, None]))[valid].all())
+    assert bool((res.corr[~valid] == -1).all())
+    # the result is a rigid planar transform
+    R = res.T[:, :2, :2]
+    eye = torch.eye(2, dtype=torch.float64, device="cuda")
+    assert float((R @ R.transpose(1, 2) - eye).abs().max()) < 1e-12
+    assert bool((res.T[:, 3] == torch.tensor([0., 0., 0., 1.], dtype=torch.float64, device="cuda")).all())
+    rng = np.random.default_rng(0)
+    _check_sample(b, res, rng.choice(4955, size=24, replace=False), 1e-3)
+    # restarting from the returned pose: point-to-point ICP never increases the error, and most
+    # pairs stop again at once (the reported error is the one BEFORE the last update)
+    res2 = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], res.T, epsilon=1e-3)
+    assert bool((res2.error <= res.error * (1 + 1e-9) + 1e-12).all())
+    assert float(res2.iters.double().median()) <= 3
+
+
+def test_batch_position_invariance():
+    """A pair's result does not depend on where it sits in the batch or what shares the launch."""
+    import lidar_slam_b200 as eng
+    from lidar_slam_b200 import synth
+    b = synth.odometry_batch(64, seed=3, device="cuda")
+    full = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
+    perm = torch.randperm(64, generator=torch.Generator().manual_seed(1)).cuda()
+    shuf = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"][perm], b["init"][perm], epsilon=1e-3)
+    assert torch.equal(shuf.T, full.T[perm]) and torch.equal(shuf.error, full.error[perm])
+    assert torch.equal(shuf.iters, full.iters[perm])
+    one = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"][17:18], b["init"][17:18], epsilon=1e-3)
+    assert torch.equal(one.T[0], full.T[17]) and int(one.iters[0]) == int(full.iters[17])
+
+
+def test_config5_shard_generated_on_device():
+    """One rank's share of the 1M-pair workload at 16 ranks (65 536 pairs, 1.1 GB of scans)."""
+    import lidar_slam_b200 as eng
+    from lidar_slam_b200 import engine, synth
+    n = 65536
+    b = synth.odometry_batch(n, seed=20 + 3, device="cuda")               # seed + rank
+    assert b["scans"].is_cuda and b["scans"].shape[0] >= n + 1
+    res = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
+    assert set(np.unique(res.status.cpu().numpy())) <= {0, 2}
+    packed = engine.pack_poses(res.T, res.error)
+    assert packed.shape == (n, 4) and bool(torch.isfinite(packed).all())
+    assert torch.equal(packed[:, 0], res.T[:, 0, 3]) and torch.equal(packed[:, 3], res.error)
+    rng = np.random.default_rng(5)
+    _check_sample(b, res, rng.choice(n, size=16, replace=False), 1e-3)
