@@ -42,15 +42,36 @@ int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
 }
 
 int launch3d(const RunParams& p, int dim, cudaStream_t stream, int sms) {
-  constexpr int R = 6, TH = 256;
+  constexpr int R = 4, TH = 256;
   auto kern = icp3d_kernel<R, TH>;
-  int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TH, 0) != cudaSuccess || per_sm < 1)
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
     return B200ICP_ERR_CUDA;
-  const long long resident = (long long)per_sm * sms;
-  const int grid = (int)(p.n_pairs < resident ? p.n_pairs : resident);
-  kern<<<grid, TH, 0, stream>>>(p, dim);
-  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+  // CTAs per pair (cluster size).  Pass counts differ a lot between pairs (2 ... hundreds), so a
+  // batch of few big clouds is bounded by its slowest pair unless that pair is spread over many
+  // SMs: grow the cluster until the batch offers ~4 CTAs per resident slot, keeping at least two
+  // rows of TH source points per CTA, at most 16 CTAs (the sm_100 cluster limit).
+  const long long rows = ((long long)p.n_max + TH - 1) / TH;
+  int g = 1;
+  while (g < 16 && (long long)p.n_pairs * g < 8LL * sms && 4LL * g <= rows) g *= 2;
+  for (; g >= 1; g /= 2) {
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = (unsigned)g; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.blockDim = dim3(TH); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cfg.attrs = &attr; cfg.numAttrs = 1;
+    cfg.gridDim = dim3((unsigned)g);
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg) != cudaSuccess || clusters < 1) {
+      cudaGetLastError();
+      continue;     // this cluster size cannot be co-scheduled: try a smaller one
+    }
+    const long long want = p.n_pairs < clusters ? p.n_pairs : clusters;
+    cfg.gridDim = dim3((unsigned)(want * g));
+    if (cudaLaunchKernelEx(&cfg, kern, p, dim) != cudaSuccess) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
+    return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+  }
+  return B200ICP_ERR_CUDA;
 }
 
 int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream) {

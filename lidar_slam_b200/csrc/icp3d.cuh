@@ -1,17 +1,23 @@
-// Fused general (3-D, or planar scans too large for the 2-D kernel) ICP: one CTA per
-// pair, clouds stay in global memory (L2 resident), the target is streamed through a
-// shared-memory fp32 tile.  Same exactness scheme as icp2d.cuh; the solve is the 3x3
-// Kabsch of kabsch3.cuh.
+// Fused general (3-D, or planar scans too large for the 2-D kernel) ICP.  One thread-block
+// CLUSTER aligns one pair: the source cloud is cut into one slice per CTA of the cluster, every
+// CTA sweeps its slice against the whole target (streamed through a shared-memory fp32 tile,
+// packed fp32x2 math), the per-pass sums are reduced CTA -> cluster through distributed shared
+// memory behind one hardware cluster barrier, and every CTA solves the same 3x3 Kabsch problem
+// redundantly so the pose never leaves registers.  The cluster size is chosen at launch from
+// the batch shape (few big clouds -> 16 CTAs per pair, many small ones -> 1).  Same exactness
+// scheme as icp2d.cuh; the solve is kabsch3.cuh.
 //
 // Replaces modules/icp.py:123-189 for the call shape of
 // code/icp_warm_up/test_icp.py:78-88 (3-D clouds, 24 yaw initialisations).
 #pragma once
+#include <cooperative_groups.h>
+
 #include "icp_common.cuh"
 #include "kabsch3.cuh"
 
 namespace b200icp {
 
-constexpr int kTile3d = 2048;   // targets per shared-memory tile (SoA fp32: 24 KB)
+constexpr int kTile3d = 2048;   // targets per shared-memory tile (fp32 [x4 y4 z4] groups: 24 KB)
 constexpr int kSums3d = 16;     // sum u(3) v(3) u v^T(9) sse
 constexpr int kRed3d = 22;      // + min/max per axis over moved source and matched target
 
@@ -33,23 +39,98 @@ struct Affine3 {  // rows 0..2 of the homogeneous transform
   }
 };
 
+// One 32-target block of the sweep for R source points per thread.  The tile holds groups of
+// four targets as [x0..x3 y0..y3 z0..z3]; every LDS.128 is a warp-wide broadcast.  Per two
+// candidates: 3 FADD2 + FMUL2 + 2 FFMA2, bit-identical to dist2_3d() (same operation order).
+template <int R>
+__device__ __forceinline__ void sweep3d_block(const float* tile_blk, const f32x2 (&qxx)[R],
+                                              const f32x2 (&qyy)[R], const f32x2 (&qzz)[R],
+                                              float (&bm)[R]) {
+  const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(tile_blk);
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    const ulonglong2 X = tp[3 * g], Y = tp[3 * g + 1], Z = tp[3 * g + 2];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      f32x2 dx = sub2(qxx[r], X.x), dy = sub2(qyy[r], Y.x), dz = sub2(qzz[r], Z.x);
+      const f32x2 d01 = fma2(dx, dx, fma2(dy, dy, mul2(dz, dz)));
+      dx = sub2(qxx[r], X.y); dy = sub2(qyy[r], Y.y); dz = sub2(qzz[r], Z.y);
+      const f32x2 d23 = fma2(dx, dx, fma2(dy, dy, mul2(dz, dz)));
+      float d0, d1, d2, d3;
+      unpack2(d01, d0, d1);
+      unpack2(d23, d2, d3);
+      bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
+    }
+  }
+}
+
+// The sweep of one chunk (NR rows of TH source points) against the whole target: the target is
+// restaged tile by tile (fp64 -> fp32) by all threads of the CTA.  NR is CTA-uniform.
+template <int NR, int R, int TH>
+__device__ __forceinline__ void sweep3d_chunk(float* tile, const double* tgt, int dim, int nt, int group,
+                                              int nblk32, const float (&qx)[R], const float (&qy)[R],
+                                              const float (&qz)[R], unsigned (&best)[R],
+                                              unsigned (&second)[R]) {
+  const int tid = threadIdx.x;
+  f32x2 qxx[NR], qyy[NR], qzz[NR];
+  float bm[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); qzz[r] = pack2(qz[r], qz[r]);
+    bm[r] = __int_as_float(0x7f800000);
+  }
+  for (int tbase = 0; tbase < nt; tbase += kTile3d) {
+    __syncthreads();
+    for (int i = tid; i < kTile3d; i += TH) {
+      float x = kBigCoord, y = kBigCoord, z = kBigCoord;
+      if (tbase + i < nt) {
+        double dx, dy, dz;
+        load_point(tgt, dim, tbase + i, dx, dy, dz);
+        x = (float)dx; y = (float)dy; z = (float)dz;
+      }
+      float* g = tile + (i >> 2) * 12 + (i & 3);
+      g[0] = x; g[4] = y; g[8] = z;
+    }
+    __syncthreads();
+    const int nb = (min(kTile3d, nt - tbase) + 31) >> 5;
+    for (int b = 0; b < nb; ++b) {
+      const int gb = (tbase >> 5) + b;
+      sweep3d_block<NR>(tile + b * 96, qxx, qyy, qzz, bm);
+      if ((gb + 1) % group == 0 || gb == nblk32 - 1) {
+        const unsigned id = (unsigned)(gb / group);
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+          const unsigned pk = (__float_as_uint(bm[r]) & 0xfffffc00u) | id;
+          second[r] = min(second[r], max(best[r], pk));
+          best[r] = min(best[r], pk);
+          bm[r] = __int_as_float(0x7f800000);
+        }
+      }
+    }
+  }
+}
+
 template <int R, int TH>
-__global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const int dim) {
-  __shared__ __align__(16) float tile_x[kTile3d];
-  __shared__ __align__(16) float tile_y[kTile3d];
-  __shared__ __align__(16) float tile_z[kTile3d];
-  __shared__ double red[2][TH / 32][kRed3d];
+__global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const int dim) {
+  __shared__ __align__(16) float tile[kTile3d * 3];     // groups of four targets: x4 y4 z4
+  __shared__ double wpart[TH / 32][kRed3d];             // per-warp partial sums of this CTA
+  __shared__ double part[2][kRed3d];                    // this CTA's sums, by pass parity (read by the cluster)
+  __shared__ double s_tot[kRed3d];                      // cluster totals
   __shared__ int s_pair;
   constexpr int W = TH / 32;
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int G = (int)cluster.num_blocks();              // CTAs per pair
+  const int rank = (int)cluster.block_rank();
   const double kInf = __longlong_as_double(0x7ff0000000000000LL);
   constexpr float kTruncRel = 2.44140625e-4f;  // 2^-12 >= the 10 truncated mantissa bits (2^-13)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   for (;;) {
-    __syncthreads();
-    if (tid == 0) s_pair = (int)atomicAdd(p.queue, 1u);
-    __syncthreads();
-    const int pair = s_pair;
+    if (rank == 0 && tid == 0) s_pair = (int)atomicAdd(p.queue, 1u);
+    cluster.sync();
+    const int pair = *cluster.map_shared_rank(&s_pair, 0);
+    cluster.sync();   // every CTA has read rank 0's s_pair: rank 0 may overwrite it, or exit
     if (pair >= p.n_pairs) break;
 
     const int si = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
@@ -62,7 +143,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
       if (ns <= 0 || nt <= 0) early = B200ICP_STATUS_EMPTY;
     }
     if (early >= 0) {
-      if (tid == 0) {
+      if (tid == 0 && rank == 0) {
         if (p.status_out) p.status_out[pair] = early;
         if (p.iters_out) p.iters_out[pair] = 0;
         if (p.err_out) p.err_out[pair] = __longlong_as_double(0x7ff8000000000000LL);
@@ -70,7 +151,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
           for (int k = 0; k < 16; ++k) p.T_out[(size_t)pair * 16 + k] = p.init ? p.init[(size_t)pair * 16 + k] : 0.0;
       }
       if (p.corr_out)
-        for (int j = tid; j < p.n_max; j += TH) p.corr_out[(size_t)pair * p.n_max + j] = -1;
+        for (int j = rank * TH + tid; j < p.n_max; j += G * TH) p.corr_out[(size_t)pair * p.n_max + j] = -1;
       continue;
     }
     const double* src = p.scans + (size_t)si * p.n_max * dim;
@@ -98,14 +179,14 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
     }
     amax = warp_maxf(amax);
     cx = warp_sum(cx); cy = warp_sum(cy); cz = warp_sum(cz);
-    if (lane == 0) { red[0][warp][0] = (double)amax; red[0][warp][1] = cx; red[0][warp][2] = cy; red[0][warp][3] = cz; }
+    if (lane == 0) { wpart[warp][0] = (double)amax; wpart[warp][1] = cx; wpart[warp][2] = cy; wpart[warp][3] = cz; }
     __syncthreads();
     float tmax = 0.f;
     double ox = 0.0, oy = 0.0, oz = 0.0;
 #pragma unroll
     for (int w = 0; w < W; ++w) {
-      tmax = fmaxf(tmax, (float)red[0][w][0]);
-      ox += red[0][w][1]; oy += red[0][w][2]; oz += red[0][w][3];
+      tmax = fmaxf(tmax, (float)wpart[w][0]);
+      ox += wpart[w][1]; oy += wpart[w][2]; oz += wpart[w][3];
     }
     tmax *= (1.0f + 4.0f * kU);
     ox /= (double)nt; oy /= (double)nt; oz /= (double)nt;
@@ -116,6 +197,11 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
     const int nblk32 = (nt + 31) >> 5;
     const int group = (nblk32 + 1023) >> 10;      // 32-target blocks per bookkeeping block
     const int bk_targets = 32 * group;
+    // source slice of this CTA: rows of TH points dealt out evenly over the cluster, processed in
+    // chunks of nr <= R rows (rows spread evenly over the chunks so that no chunk is nearly empty)
+    const int rows_total = (ns + TH - 1) / TH;
+    const int row_lo = (int)((long long)rows_total * rank / G), row_hi = (int)((long long)rows_total * (rank + 1) / G);
+    const int n_chunks = (row_hi - row_lo + R - 1) / R;
     StopState st{0.0, 0, 0};
     int passes = 0;
 
@@ -126,7 +212,11 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
 #pragma unroll
       for (int k = 0; k < 3; ++k) { acc[kSums3d + 2 * k] = kInf; acc[kSums3d + 2 * k + 1] = -kInf; }
 
-      for (int cbase = 0; cbase < ns; cbase += TH * R) {
+      for (int ch = 0; ch < n_chunks; ++ch) {
+        const int rows_here = row_hi - row_lo;
+        const int row0 = row_lo + (int)((long long)rows_here * ch / n_chunks);
+        const int nr = row_lo + (int)((long long)rows_here * (ch + 1) / n_chunks) - row0;
+        const int cbase = row0 * TH;
         float qx[R], qy[R], qz[R];
         unsigned best[R], second[R];
 #pragma unroll
@@ -134,7 +224,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
           const int j = cbase + tid + TH * r;
           qx[r] = qy[r] = qz[r] = 0.f;
           best[r] = second[r] = 0xffffffffu;
-          if (j < ns) {
+          if (r < nr && j < ns) {
             double sx, sy, sz, x, y, z;
             load_point(src, dim, j, sx, sy, sz);
             T.apply(sx, sy, sz, x, y, z);
@@ -142,50 +232,12 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
           }
         }
         // ---- fp32 sweep, target streamed through the shared tile ----------------
-        float bm[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) bm[r] = __int_as_float(0x7f800000);
-        for (int tbase = 0; tbase < nt; tbase += kTile3d) {
-          __syncthreads();
-          for (int i = tid; i < kTile3d; i += TH) {
-            float x = kBigCoord, y = kBigCoord, z = kBigCoord;
-            if (tbase + i < nt) {
-              double dx, dy, dz;
-              load_point(tgt, dim, tbase + i, dx, dy, dz);
-              x = (float)dx; y = (float)dy; z = (float)dz;
-            }
-            tile_x[i] = x; tile_y[i] = y; tile_z[i] = z;
-          }
-          __syncthreads();
-          const int nb = (min(kTile3d, nt - tbase) + 31) >> 5;
-          for (int b = 0; b < nb; ++b) {
-            const int gb = (tbase >> 5) + b;
-            const float4* vx = reinterpret_cast<const float4*>(tile_x + b * 32);
-            const float4* vy = reinterpret_cast<const float4*>(tile_y + b * 32);
-            const float4* vz = reinterpret_cast<const float4*>(tile_z + b * 32);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float4 X = vx[i], Y = vy[i], Z = vz[i];
-#pragma unroll
-              for (int r = 0; r < R; ++r) {
-                const float d0 = dist2_3d(qx[r], qy[r], qz[r], X.x, Y.x, Z.x);
-                const float d1 = dist2_3d(qx[r], qy[r], qz[r], X.y, Y.y, Z.y);
-                const float d2 = dist2_3d(qx[r], qy[r], qz[r], X.z, Y.z, Z.z);
-                const float d3 = dist2_3d(qx[r], qy[r], qz[r], X.w, Y.w, Z.w);
-                bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
-              }
-            }
-            if ((gb + 1) % group == 0 || gb == nblk32 - 1) {
-              const unsigned id = (unsigned)(gb / group);
-#pragma unroll
-              for (int r = 0; r < R; ++r) {
-                const unsigned pk = (__float_as_uint(bm[r]) & 0xfffffc00u) | id;
-                second[r] = min(second[r], max(best[r], pk));
-                best[r] = min(best[r], pk);
-                bm[r] = __int_as_float(0x7f800000);
-              }
-            }
-          }
+        switch (nr) {
+          case 1: sweep3d_chunk<1, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 2: if constexpr (R >= 2) sweep3d_chunk<2, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 3: if constexpr (R >= 3) sweep3d_chunk<3, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 4: if constexpr (R >= 4) sweep3d_chunk<4, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
+          default: break;
         }
         // ---- exact resolution ------------------------------------------------------
         int corr[R];
@@ -194,7 +246,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
         for (int r = 0; r < R; ++r) {
           const int j = cbase + tid + TH * r;
           corr[r] = -1;
-          if (j < ns) {
+          if (r < nr && j < ns) {
             const int blk = (int)(best[r] & 1023u);
             const float bval = __uint_as_float(best[r] & 0xfffffc00u);
             const float sval = __uint_as_float(second[r] & 0xfffffc00u);
@@ -258,7 +310,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const int j = cbase + tid + TH * r;
-          if (j < ns) {
+          if (r < nr && j < ns) {
             double sx, sy, sz, x, y, z, ax, ay, az;
             load_point(src, dim, j, sx, sy, sz);
             T.apply(sx, sy, sz, x, y, z);
@@ -293,24 +345,37 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
           acc[kSums3d + 2 * k + 1] = warp_max(acc[kSums3d + 2 * k + 1]);
         }
       }
-      double(*slot)[kRed3d] = red[passes & 1];
+      // CTA: warp partials -> part[parity]; cluster: every CTA adds the G parts in rank order
+      // (distributed shared memory), so all CTAs hold bit-identical totals and take the same
+      // decisions.  Entries 16/18/20 are minima, 17/19/21 maxima, the rest sums.
       if (lane == 0) {
 #pragma unroll
-        for (int k = 0; k < kRed3d; ++k) slot[warp][k] = acc[k];
+        for (int k = 0; k < kRed3d; ++k) wpart[warp][k] = acc[k];
+      }
+      __syncthreads();
+      const bool is_min = lane >= kSums3d && ((lane - kSums3d) & 1) == 0;
+      const bool is_max = lane >= kSums3d && ((lane - kSums3d) & 1) == 1;
+      if (warp == 0 && lane < kRed3d) {
+        double v = wpart[0][lane];
+        for (int w = 1; w < W; ++w) {
+          const double o = wpart[w][lane];
+          v = is_min ? fmin(v, o) : (is_max ? fmax(v, o) : v + o);
+        }
+        part[passes & 1][lane] = v;
+      }
+      cluster.sync();
+      if (warp == 0 && lane < kRed3d) {
+        double v = *cluster.map_shared_rank(&part[passes & 1][lane], 0);
+        for (int g = 1; g < G; ++g) {
+          const double o = *cluster.map_shared_rank(&part[passes & 1][lane], g);
+          v = is_min ? fmin(v, o) : (is_max ? fmax(v, o) : v + o);
+        }
+        s_tot[lane] = v;
       }
       __syncthreads();
       double tot[kRed3d];
 #pragma unroll
-      for (int k = 0; k < kRed3d; ++k) tot[k] = slot[0][k];
-      for (int w = 1; w < W; ++w) {
-#pragma unroll
-        for (int k = 0; k < kSums3d; ++k) tot[k] += slot[w][k];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          tot[kSums3d + 2 * k] = fmin(tot[kSums3d + 2 * k], slot[w][kSums3d + 2 * k]);
-          tot[kSums3d + 2 * k + 1] = fmax(tot[kSums3d + 2 * k + 1], slot[w][kSums3d + 2 * k + 1]);
-        }
-      }
+      for (int k = 0; k < kRed3d; ++k) tot[k] = s_tot[k];
       passes += 1;
 
       double err = tot[15];
@@ -349,7 +414,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
         status = stop_test(st, err, epsilon, p.max_iters, p.stopping_thresh);
       }
       if (status >= 0) {
-        if (tid == 0) {
+        if (tid == 0 && rank == 0) {
           if (p.T_out) {
             double* To = p.T_out + (size_t)pair * 16;
 #pragma unroll
@@ -361,7 +426,7 @@ __global__ void __launch_bounds__(TH, 1) icp3d_kernel(const RunParams p, const i
           if (p.iters_out) p.iters_out[pair] = passes;
           if (p.status_out) p.status_out[pair] = status;
         }
-        if (p.corr_out)
+        if (p.corr_out && rank == 0)
           for (int j = ns + tid; j < p.n_max; j += TH) p.corr_out[(size_t)pair * p.n_max + j] = -1;
         break;
       }
