@@ -216,13 +216,38 @@ def run_b200_arm(args):
         host.append({n: t.cpu().pin_memory() for n, t in pl.items()})
     h2d_bytes = sum(t.numel() * t.element_size() for t in host[0].values())
     gathered = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
+    # multi-GPU pose exchange: fused peer stores from the ICP kernel's epilogue into every rank's
+    # symmetric-memory buffer (NVLink), or -- if symmetric memory is unavailable -- pack + NCCL.
+    peer = None
+    if world > 1 and args.exchange in ("auto", "peer"):
+        try:
+            gathered, peer = engine._peer_gather_buffer(world * B, dev, None)
+        except Exception as exc:               # noqa: BLE001
+            if args.exchange == "peer":
+                raise
+            sys.stderr.write(f"[bench] symmetric memory unavailable ({exc!r}); using NCCL all-gather\n")
+            peer = None
+        flag = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)          # all ranks must agree on the mode
+        if int(flag.item()) == 0:
+            peer = None
+            gathered = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
     host_out = torch.empty((world * B, 4), dtype=torch.float64).pin_memory()
     d2h_bytes = host_out.numel() * host_out.element_size()
 
+    def exchange_kw():
+        return dict(peer_pose_ptrs=list(peer.buffer_ptrs), peer_row0=rank * B) if peer is not None else {}
+
     def step_device(k):
         pl = pools[k % N_POOLS]
+        if peer is not None:
+            peer.barrier(channel=0)            # the previous step's rows have been consumed everywhere
         res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
-                                   max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False)
+                                   max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False,
+                                   **exchange_kw())
+        if peer is not None:
+            peer.barrier(channel=1)            # every rank's rows have landed in every buffer
+            return res
         poses = engine.pack_poses(res.T, res.error)
         if world > 1:
             dist.all_gather_into_tensor(gathered, poses)
@@ -232,8 +257,15 @@ def run_b200_arm(args):
 
     def step_e2e(k):
         hp = host[k % N_POOLS]          # HOST buffers in, HOST poses out, every step
+        if peer is not None:
+            peer.barrier(channel=0)
         res = engine.run_icp_batch(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
-                                   max_iters=MAX_ITERS, stopping_thresh=STOP)
+                                   max_iters=MAX_ITERS, stopping_thresh=STOP, **exchange_kw())
+        if peer is not None:
+            peer.barrier(channel=1)
+            host_out.copy_(gathered, non_blocking=True)
+            torch.cuda.synchronize()
+            return
         poses = engine.pack_poses(res.T, res.error)
         if world > 1:
             dist.all_gather_into_tensor(gathered, poses)
@@ -272,6 +304,16 @@ def run_b200_arm(args):
         cand.append(float((res.iters.double() * cn[pr[:, 0]] * cn[pr[:, 1]]).sum().item()))
     mean_passes = float(sum(r.iters.double().mean().item() for r in results.values()) / N_POOLS)
     ok = all(bool(((r.status == 0) | (r.status == 2)).all().item()) for r in results.values())
+    # the exchange delivered this rank's rows intact and every other rank's rows are finite
+    last = results[(max(args.warmup, N_POOLS) - 1) % N_POOLS]
+    mine = engine.pack_poses(last.T, last.error)
+    exchange_ok = bool(torch.equal(gathered[rank * B:(rank + 1) * B], mine)) and bool(torch.isfinite(gathered).all())
+    if world > 1:
+        flag = torch.tensor([1 if exchange_ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        exchange_ok = bool(flag.item())
+    if not exchange_ok:
+        raise RuntimeError("pose exchange mismatch: gathered rows differ from the local results")
 
     # ---- timed region 1: inputs resident in HBM ----
     sampler = ClockSampler(local)
@@ -355,11 +397,15 @@ def run_b200_arm(args):
                    "pairs_per_gpu": B, "points_per_scan": "1081 beams, ~1075 valid", "epsilon": EPSILON,
                    "max_iters": MAX_ITERS, "stopping_thresh": STOP, "mean_passes_per_pair": mean_passes,
                    "l2": f"{N_POOLS} distinct scan pools of 85.7 MB rotated between steps (171 MB > 126 MB L2)",
-                   "exchange": "one NCCL all_gather_into_tensor of [B,4] f64 per step" if world > 1 else "none (1 GPU)",
+                   "exchange": ("none (1 GPU)" if world == 1 else
+                                "fused: peer stores of [B,4] f64 rows from the ICP kernel epilogue into every rank's "
+                                "symmetric-memory buffer over NVLink + 2 cross-rank barriers per step"
+                                if peer is not None else "pack_poses + one NCCL all_gather_into_tensor of [B,4] f64 per step"),
                    "all_pairs_converged": ok},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                 "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": 2 * args.steps,     # icp2d_kernel + pack_poses_kernel per step
+        # icp2d_kernel per step, plus pack_poses_kernel when the exchange is not fused into it
+        "gpu_launches": (1 if peer is not None else 2) * args.steps,
         "roofline": roofline,
         "clocks": clocks,
     }
@@ -409,6 +455,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step (default: config 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
+                    help="multi-GPU pose exchange: fused peer stores (symmetric memory) or NCCL all-gather")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -91,6 +91,24 @@ int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_m
                 double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                 int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* b200icp_run with the multi-GPU pose exchange fused into the kernel epilogue: the thread that
+ * finishes pair b also stores its packed row (x, y, theta, error) -- the b200icp_pack_poses
+ * layout -- into row peer_row0 + b of each of the n_peers gather buffers.  The buffers are
+ * peer-mapped device memory of every rank (this rank's own included), e.g. the buffer_ptrs of a
+ * torch symmetric-memory allocation, so the rows travel as plain stores over NVLink / NVSwitch
+ * while the rest of the batch is still being aligned; no separate gather kernel or collective
+ * runs afterwards, only a cross-rank barrier before the rows are read.  This is what returns the
+ * relative poses to the pose-graph builder on every rank (main.py:148-172).
+ * peer_pose_out: HOST array of n_peers (<= 16) device pointers, each 32-byte aligned and holding
+ * at least peer_row0 + n_pairs rows of 4 float64.  Pairs that are not run (status 4/5/6) store
+ * the pose of their init with a NaN error. */
+int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                         const int32_t* pairs, const double* init, const double* epsilon,
+                         const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                         double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                         int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
+                         double* const* peer_pose_out, int n_peers, long long peer_row0);
+
 /* One exact nearest-neighbour pass, exposed on its own for tests and for the
  * roofline measurement.  Replaces get_correspondences / KDTree.query
  * (modules/icp.py:29-41 with :161) for a batch of (query set, target set) pairs

@@ -21,6 +21,10 @@ SIGNATURES = {
     "b200icp_run": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200icp_run_exchange": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_int,
+                                     ctypes.c_longlong]),
     "b200icp_nearest": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),
     "b200icp_pack_poses": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),

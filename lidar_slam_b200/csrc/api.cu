@@ -150,19 +150,48 @@ int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out) 
   return B200ICP_OK;
 }
 
-int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
-                const int32_t* pairs, const double* init, const double* epsilon,
-                const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
-                double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
-                int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream) {
+static int run_common(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                      const int32_t* pairs, const double* init, const double* epsilon,
+                      const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                      double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                      int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
+                      double* const* peer_pose_out, int n_peers, long long peer_row0) {
   if (!init || !epsilon || !normalize || !T_out || max_iters < 0) return B200ICP_ERR_BAD_ARG;
+  if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && !peer_pose_out) || peer_row0 < 0)
+    return B200ICP_ERR_BAD_ARG;
   RunParams p{};
   p.scans = scans; p.counts = counts; p.n_scans = n_scans; p.n_max = n_max;
   p.pairs = pairs; p.init = init; p.epsilon = epsilon; p.normalize = normalize;
   p.n_pairs = n_pairs; p.max_iters = max_iters; p.stopping_thresh = stopping_thresh;
   p.T_out = T_out; p.err_out = err_out; p.iters_out = iters_out; p.status_out = status_out;
   p.corr_out = corr_out; p.dist2_out = nullptr; p.nearest_only = 0;
+  p.n_peers = n_peers; p.peer_row0 = peer_row0;
+  for (int k = 0; k < n_peers; ++k) {
+    if (!peer_pose_out[k] || (reinterpret_cast<uintptr_t>(peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
+    p.peer_out[k] = peer_pose_out[k];
+  }
   return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                const int32_t* pairs, const double* init, const double* epsilon,
+                const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream) {
+  return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
+                    stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
+                    workspace_bytes, stream, nullptr, 0, 0);
+}
+
+int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                         const int32_t* pairs, const double* init, const double* epsilon,
+                         const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                         double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                         int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
+                         double* const* peer_pose_out, int n_peers, long long peer_row0) {
+  return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
+                    stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
+                    workspace_bytes, stream, peer_pose_out, n_peers, peer_row0);
 }
 
 int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,

@@ -149,6 +149,10 @@ __global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const i
         if (p.err_out) p.err_out[pair] = __longlong_as_double(0x7ff8000000000000LL);
         if (p.T_out)
           for (int k = 0; k < 16; ++k) p.T_out[(size_t)pair * 16 + k] = p.init ? p.init[(size_t)pair * 16 + k] : 0.0;
+        if (p.init) {
+          const double* T0 = p.init + (size_t)pair * 16;
+          store_pose_to_peers(p, pair, T0[3], T0[7], T0[0], T0[4], __longlong_as_double(0x7ff8000000000000LL));
+        }
       }
       if (p.corr_out)
         for (int j = rank * TH + tid; j < p.n_max; j += G * TH) p.corr_out[(size_t)pair * p.n_max + j] = -1;
@@ -425,6 +429,7 @@ __global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const i
           if (p.err_out) p.err_out[pair] = err;
           if (p.iters_out) p.iters_out[pair] = passes;
           if (p.status_out) p.status_out[pair] = status;
+          store_pose_to_peers(p, pair, T.m[3], T.m[7], T.m[0], T.m[4], err);
         }
         if (p.corr_out && rank == 0)
           for (int j = ns + tid; j < p.n_max; j += TH) p.corr_out[(size_t)pair * p.n_max + j] = -1;

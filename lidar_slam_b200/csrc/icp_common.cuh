@@ -190,6 +190,8 @@ __device__ __forceinline__ int stop_test(StopState& st, double err, double epsil
   return -1;
 }
 
+constexpr int kMaxPeers = 16;
+
 struct RunParams {
   const double* scans;
   const int32_t* counts;
@@ -208,6 +210,25 @@ struct RunParams {
   double* dist2_out;      // nearest-only mode
   int nearest_only;       // 1: single NN pass on untransformed queries, no solve
   unsigned int* queue;    // work counter in the workspace (zeroed before launch)
+  // fused pose exchange (multi-GPU): when n_peers > 0 the thread that finishes pair b also
+  // stores its packed pose row (x, y, theta, error) into row peer_row0 + b of every rank's
+  // gather buffer -- peer-mapped device pointers, i.e. plain stores that travel over NVLink.
+  double* peer_out[kMaxPeers];
+  int n_peers;
+  long long peer_row0;
 };
+
+// kept out of line: atan2's slow path must not widen the register footprint of the ICP loops
+__device__ __noinline__ double pose_angle(double r10, double r00) { return atan2(r10, r00); }
+
+// pose_from_T(TSE2_from_TSE3(T)) (modules/utils.py:196-225) + error, to every peer buffer
+__device__ __forceinline__ void store_pose_to_peers(const RunParams& p, int pair, double x, double y,
+                                                    double r00, double r10, double err) {
+  if (p.n_peers <= 0) return;
+  double4 row;
+  row.x = x; row.y = y; row.z = pose_angle(r10, r00); row.w = err;
+  for (int k = 0; k < p.n_peers; ++k)
+    reinterpret_cast<double4*>(p.peer_out[k])[p.peer_row0 + pair] = row;
+}
 
 }  // namespace b200icp

@@ -100,7 +100,7 @@ def _per_pair(x, n, dtype, dev):
 
 def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_iters=2000,
                   stopping_thresh=0.0001, normalize_error=False, return_correspondences=False,
-                  planar_fallback=True) -> IcpBatchResult:
+                  planar_fallback=True, peer_pose_ptrs=None, peer_row0=0) -> IcpBatchResult:
     """Align every (source, target) pair of `pairs` in one launch.
 
     scans  [S, n_max, D] float64 (D = 2 or 3), counts [S] int32 (see pack_scans);
@@ -109,6 +109,9 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     epsilon, normalize_error: scalar or length-B (so that odometry pairs and
     loop-closure pairs with different settings share one launch);
     max_iters, stopping_thresh: scalars, as modules/icp.py:128-129.
+    peer_pose_ptrs: optional list of peer-mapped device pointers (one gather buffer per rank);
+    the kernel then also stores every pair's (x, y, theta, error) row into row peer_row0 + b of
+    each buffer (b200icp_run_exchange; see run_icp_sharded).
     """
     lib = _lib.load()
     dev = scans.device if isinstance(scans, torch.Tensor) and scans.is_cuda else _device()
@@ -152,6 +155,15 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
 
     def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax):
         with torch.cuda.device(dev):
+            if peer_pose_ptrs:
+                peers = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
+                _lib.check(lib.b200icp_run_exchange(
+                    _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
+                    _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
+                    _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
+                    _stream_ptr(), ctypes.cast(peers, ctypes.c_void_p), len(peer_pose_ptrs), int(peer_row0)),
+                    "b200icp_run_exchange")
+                return
             _lib.check(lib.b200icp_run(
                 _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
                 _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
@@ -190,12 +202,35 @@ def shard_range(n_items: int, rank: int, world: int):
     return lo, min(lo + per, n_items), per
 
 
-def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, **kw):
-    """Multi-GPU entry: every rank holds the scan pool (or at least the scans its pairs use),
-    aligns its contiguous shard of `pairs`, and ONE all-gather (NCCL over NVLink on GPUs, gloo
-    in the CPU tests of the host logic) returns [B,4] (x, y, theta, error) rows for all pairs,
-    in pair order, on every rank -- what the pose-graph builder needs (main.py:148-172).
-    Pairs are independent, so there is no other exchange.
+_PEER_BUFFERS = {}
+
+
+def _peer_gather_buffer(rows: int, dev, group):
+    """Symmetric-memory gather buffer [rows, 4] float64 shared by all ranks of `group` (cached):
+    every rank maps every other rank's copy, so a kernel can store straight into it over NVLink."""
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm_mem
+    key = (rows, str(dev), id(group))
+    if key not in _PEER_BUFFERS:
+        buf = symm_mem.empty((rows, 4), dtype=torch.float64, device=dev)
+        hdl = symm_mem.rendezvous(buf, group=group if group is not None else dist.group.WORLD)
+        _PEER_BUFFERS[key] = (buf, hdl)
+    return _PEER_BUFFERS[key]
+
+
+def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, exchange="auto", **kw):
+    """Multi-GPU entry: every rank holds the scan pool (or at least the scans its pairs use) and
+    aligns its contiguous shard of `pairs`; the [B,4] (x, y, theta, error) rows of ALL pairs, in
+    pair order, end up on every rank -- what the pose-graph builder needs (main.py:148-172).
+    Pairs are independent, so this is the only exchange.
+
+    exchange="peer": fused -- the ICP kernel's epilogue stores each finished row directly into
+    every rank's symmetric-memory gather buffer (peer stores over NVLink / NVSwitch), followed by
+    one cross-rank barrier; no gather kernel, no collective.  exchange="nccl": pack_poses + ONE
+    all_gather_into_tensor (NCCL on GPUs, gloo in the CPU tests of the host logic).
+    "auto" = "peer" on CUDA with NCCL when symmetric memory is available, else "nccl".
+    Returns (rows [B,4], local IcpBatchResult); with "peer" the rows alias the cached buffer and
+    are valid until the next sharded call of the same shape.
     """
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -209,6 +244,23 @@ def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, **kw
         v = kw.get(key)
         if v is not None and not isinstance(v, (int, float, bool)):
             kw[key] = v[lo:hi]
+    use_peer = False
+    if world > 1 and exchange in ("auto", "peer") and torch.cuda.is_available() and dist.get_backend(group) == "nccl":
+        try:
+            buf, hdl = _peer_gather_buffer(world * per, _device(), group)
+            use_peer = True
+        except Exception:                      # symmetric memory unavailable on this build / topology
+            if exchange == "peer":
+                raise
+    if use_peer:
+        hdl.barrier(channel=0)                 # nobody still reads the previous contents
+        res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, peer_pose_ptrs=list(hdl.buffer_ptrs),
+                            peer_row0=rank * per, **kw)
+        if hi - lo < per:                      # this rank's padding rows, to every peer
+            for r in range(world):
+                hdl.get_buffer(r, (world * per, 4), torch.float64)[rank * per + (hi - lo):(rank + 1) * per] = float("nan")
+        hdl.barrier(channel=1)                 # every rank's rows have landed everywhere
+        return buf[:n], res
     res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, **kw)
     local = torch.full((per, 4), float("nan"), dtype=torch.float64, device=res.T.device)
     if hi > lo:
