@@ -8,6 +8,7 @@ PyTorch is used for device memory and streams only.
 from __future__ import annotations
 
 import ctypes
+import os
 from dataclasses import dataclass
 from typing import Optional, Sequence, Union
 
@@ -98,6 +99,55 @@ def _per_pair(x, n, dtype, dev):
     return t
 
 
+_PIPELINE_MIN_PAIRS = 2048
+_PIPELINE_CHUNKS = int(os.environ.get("B200ICP_PIPELINE_CHUNKS", "6"))
+_SIDE_STREAMS = {}
+
+
+def _side_streams(dev):
+    key = str(dev)
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = [torch.cuda.Stream(device=dev) for _ in range(3)]     # copy, compute A, compute B
+    return _SIDE_STREAMS[key]
+
+
+def _copy_pool_pipelined(host_pool, dev_pool, pairs_host, dev, launch_chunk):
+    """Host -> device copy of the scan pool overlapped with the alignment: the pair list is cut
+    into chunks; before chunk c runs, the prefix of the pool it references (rows up to its
+    largest scan index) has been copied on the copy stream; chunks alternate between two
+    compute streams so that one chunk's queue tail overlaps the next chunk's start.
+    launch_chunk(lo, hi, workspace) launches pairs [lo, hi) on the current stream; None = copy only."""
+    cur = torch.cuda.current_stream(dev)
+    copy_s, comp_a, comp_b = _side_streams(dev)
+    n_pairs, n_scans = pairs_host.shape[0], host_pool.shape[0]
+    k = _PIPELINE_CHUNKS if launch_chunk is not None else 1
+    bounds = [n_pairs * c // k for c in range(k + 1)]
+    copy_s.wait_stream(cur)
+    comp_a.wait_stream(cur)
+    comp_b.wait_stream(cur)
+    copied = 0
+    for c in range(k):
+        lo, hi = bounds[c], bounds[c + 1]
+        need = n_scans if (launch_chunk is None or c == k - 1) else min(n_scans, int(pairs_host[lo:hi].max()) + 1)
+        with torch.cuda.stream(copy_s):
+            if need > copied:
+                dev_pool[copied:need].copy_(host_pool[copied:need], non_blocking=True)
+                copied = need
+            ready = torch.cuda.Event()
+            ready.record(copy_s)
+        if launch_chunk is None or hi <= lo:
+            continue
+        st = comp_a if c % 2 == 0 else comp_b
+        st.wait_event(ready)
+        with torch.cuda.stream(st):
+            ws_c = torch.empty((256,), dtype=torch.uint8, device=dev)
+            ws_c.record_stream(st)
+            launch_chunk(lo, hi, ws_c)
+    cur.wait_stream(copy_s)
+    cur.wait_stream(comp_a)
+    cur.wait_stream(comp_b)
+
+
 def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_iters=2000,
                   stopping_thresh=0.0001, normalize_error=False, return_correspondences=False,
                   planar_fallback=True, peer_pose_ptrs=None, peer_row0=0) -> IcpBatchResult:
@@ -115,13 +165,27 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     """
     lib = _lib.load()
     dev = scans.device if isinstance(scans, torch.Tensor) and scans.is_cuda else _device()
-    scans = _to_dev(scans, torch.float64, dev)
+    # Host inputs in pinned memory and a big batch: the scan pool is streamed to the device in
+    # slices on a copy stream while earlier chunks of the pair list are already being aligned.
+    host_pool = None
+    if (isinstance(scans, torch.Tensor) and not scans.is_cuda and scans.is_pinned() and scans.dtype == torch.float64
+            and scans.is_contiguous() and scans.dim() == 3 and not (isinstance(pairs, torch.Tensor) and pairs.is_cuda)):
+        n_host_pairs = int(np.asarray(pairs).reshape(-1, 2).shape[0]) if not isinstance(pairs, torch.Tensor) \
+            else int(pairs.reshape(-1, 2).shape[0])
+        if n_host_pairs >= _PIPELINE_MIN_PAIRS:
+            host_pool = scans
+            scans = torch.empty(host_pool.shape, dtype=torch.float64, device=dev)     # filled slice by slice below
+    if host_pool is None:
+        scans = _to_dev(scans, torch.float64, dev)
     if scans.dim() != 3 or scans.shape[2] not in (2, 3):
         raise ValueError("scans must have shape [S, n_max, 2|3]")
     n_scans, n_max, dim = scans.shape
     if (n_max * dim) % 2:
         raise ValueError("n_max*dim must be even (16-byte aligned rows); use pack_scans")
     counts = _to_dev(counts, torch.int32, dev)
+    pairs_host = None
+    if host_pool is not None:
+        pairs_host = (pairs.numpy() if isinstance(pairs, torch.Tensor) else np.asarray(pairs)).reshape(-1, 2)
     pairs = _to_dev(pairs, torch.int32, dev).reshape(-1, 2)
     n_pairs = pairs.shape[0]
     planar_ok = True
@@ -153,7 +217,7 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     _lib.check(lib.b200icp_workspace_bytes(n_pairs, n_max, dim, ctypes.byref(nbytes)), "b200icp_workspace_bytes")
     ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
 
-    def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax):
+    def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax, ws=ws, row0=0):
         with torch.cuda.device(dev):
             if peer_pose_ptrs:
                 peers = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
@@ -161,7 +225,7 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
                     _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
                     _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
                     _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
-                    _stream_ptr(), ctypes.cast(peers, ctypes.c_void_p), len(peer_pose_ptrs), int(peer_row0)),
+                    _stream_ptr(), ctypes.cast(peers, ctypes.c_void_p), len(peer_pose_ptrs), int(peer_row0) + row0),
                     "b200icp_run_exchange")
                 return
             _lib.check(lib.b200icp_run(
@@ -170,6 +234,14 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
                 _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
                 _stream_ptr()), "b200icp_run")
 
+    if host_pool is not None:
+        _copy_pool_pipelined(host_pool, scans, pairs_host, dev,
+                             None if (dim == 2 and planar_fallback and not planar_ok) else
+                             (lambda lo, hi, ws_c: launch(dim, scans, pairs[lo:hi], init[lo:hi], eps[lo:hi], norm[lo:hi],
+                                                          T[lo:hi], err[lo:hi], iters[lo:hi], status[lo:hi],
+                                                          None if corr is None else corr[lo:hi], n_max, ws=ws_c, row0=lo)))
+        if not (dim == 2 and planar_fallback and not planar_ok):
+            return IcpBatchResult(T, err, iters, status, corr)
     if dim == 2 and planar_fallback and not planar_ok:
         # An initial transform that leaves the plane: the reference lifts the scans to z = 0 and
         # carries on in 3-D (icp.py:153-156), so the whole batch goes through the general kernel

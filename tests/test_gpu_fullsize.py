@@ -84,3 +84,27 @@ def test_config5_shard_generated_on_device():
     assert torch.equal(packed[:, 0], res.T[:, 0, 3]) and torch.equal(packed[:, 3], res.error)
     rng = np.random.default_rng(5)
     _check_sample(b, res, rng.choice(n, size=16, replace=False), 1e-3)
+
+
+def test_pipelined_host_inputs_equal_resident_inputs():
+    """Pinned host buffers take the streamed path (pool copied in slices on a copy stream while
+    earlier pair chunks run on two compute streams): bit-identical to device-resident inputs."""
+    import lidar_slam_b200 as eng
+    from lidar_slam_b200 import synth
+    b = synth.odometry_batch(4955, seed=21, device="cuda")
+    want = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, return_correspondences=True)
+    host = {k: b[k].cpu().pin_memory() for k in ("scans", "counts", "pairs", "init")}
+    for pairs in (host["pairs"], host["pairs"].flip(0).contiguous()):       # sorted and reversed pair lists
+        init = host["init"] if pairs is host["pairs"] else host["init"].flip(0).contiguous()
+        got = eng.run_icp_batch(host["scans"], host["counts"], pairs, init, epsilon=1e-3, return_correspondences=True)
+        torch.cuda.synchronize()
+        ref = want if pairs is host["pairs"] else IcpFlip(want)
+        assert torch.equal(got.T, ref.T) and torch.equal(got.error, ref.error)
+        assert torch.equal(got.iters, ref.iters) and torch.equal(got.status, ref.status)
+        assert torch.equal(got.corr, ref.corr)
+
+
+class IcpFlip:
+    def __init__(self, r):
+        self.T, self.error, self.iters, self.status, self.corr = (r.T.flip(0), r.error.flip(0), r.iters.flip(0),
+                                                                  r.status.flip(0), r.corr.flip(0))
