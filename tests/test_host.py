@@ -170,3 +170,38 @@ def test_sharded_all_gather_world2_gloo(tmp_path):
     p1 = np.load(tmp_path / "poses1.npy")
     assert p0.shape == (5, 4) and np.array_equal(p0, p1)
     np.testing.assert_allclose(p0, want, rtol=0, atol=1e-12)
+
+
+def test_c_abi_argument_validation_without_a_device():
+    """Every entry rejects bad arguments with B200ICP_ERR_BAD_ARG / _WORKSPACE / _TOO_LARGE before it
+    touches a device (no compute call is made here), and the new product modules fail loudly on a
+    box without a GPU."""
+    from lidar_slam_b200 import _lib
+    lib = _lib.load()
+    n = ctypes.c_size_t()
+    null = ctypes.c_void_p(0)
+    one = ctypes.c_void_p(64)            # never dereferenced: the calls fail on other arguments first
+    assert lib.b200icp_run(null, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256, null) == -1
+    assert lib.b200icp_run(one, one, 1, 2, 2, one, one, one, one, 1, -1, 1e-4, one, one, one, one, null, one, 256, null) == -1
+    assert lib.b200icp_run_exchange(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
+                                    null, null, 3, 0) == -1                      # peers announced but no array
+    assert lib.b200icp_run_exchange(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
+                                    null, one, 17, 0) == -1                      # more than 16 peers
+    assert lib.b200icp_scans_from_ranges(one, 1, 1081, one, one, 0.1, 30.0, 0.1, 0.0, one, one, 1081, null) == -1   # odd n_max
+    assert lib.b200icp_range_filter_workspace_bytes(ctypes.byref(n)) == 0 and n.value > 0
+    assert lib.b200icp_range_filter(one, one, 1, 1082, 3.0, one, null, 0, null) == -3
+    assert lib.b200icp_ogm_workspace_bytes(100, 100, 1082, 1, ctypes.byref(n)) == 0 and n.value > 100 * 100 * 4
+    assert lib.b200icp_ogm_build(one, 100, 100, 0.0, 0.0, 0.0, one, one, one, one, 1, 1082, 1, one, 1 << 30, null) == -1
+    assert lib.b200icp_ogm_build(one, 100, 100, 0.05, 0.0, 0.0, one, one, one, one, 1, 40000, 1, one, 1 << 30, null) == -1
+    assert lib.b200icp_ogm_build(one, 100, 100, 0.05, 0.0, 0.0, one, one, one, one, 1, 1082, 1, one, 16, null) == -3
+    assert lib.b200icp_texture_paint(one, 10, 10, 0.05, 0.0, 0.0, one, one, 1, 2048, 2048, 0, one, one, one, one, null) == -2
+    assert lib.b200icp_texture_paint(one, 10, 10, 0.05, 0.0, 0.0, one, one, 1, 48, 64, -1, one, one, one, one, null) == -1
+    assert lib.b200icp_texture_resolve(null, null, one, 10, 10, null) == -1
+    if not torch.cuda.is_available():
+        from lidar_slam_b200 import ogm, scans, texture_mapping
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            scans.scans_from_ranges(np.ones((2, 8)), 0.1, 30.0)
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            ogm.OccupancyGridMap(0.1, 1, 1, -1, -1)
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            texture_mapping.TexturePainter(10, 10, 0.1, 0, 0, np.eye(4), np.eye(3))

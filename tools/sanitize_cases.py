@@ -1,0 +1,34 @@
+"""Tiny run of every kernel for compute-sanitizer (memcheck):  compute-sanitizer --tool memcheck python tools/sanitize_cases.py"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import lidar_slam_b200 as eng
+from lidar_slam_b200 import synth, ogm, scans, texture_mapping as tm, engine
+from oracle import texture_oracle as to
+
+b = synth.odometry_batch(24, seed=5, device="cuda")
+r = eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, return_correspondences=True)
+ts, tc = synth.thin_scans(b["scans"][:8].cpu(), b["counts"][:8].cpu(), seed=3)
+eng.run_icp_batch(ts.cuda(), tc.cuda(), b["pairs"][:6], b["init"][:6], epsilon=1e-3, normalize_error=True)
+engine.pack_poses(r.T, r.error)
+src = synth.drill_cloud(1500, seed=1)
+tgts = [synth.partial_view(src, seed=10 + k) for k in range(2)]
+pool, counts = eng.pack_scans([src] + tgts)
+pairs = torch.tensor([(0, 1), (0, 2), (0, 1)], dtype=torch.int32).cuda()
+inits = torch.tensor(np.stack([synth.yaw_sweep_inits(src, tgts[0], 24)[k] for k in (0, 5, 9)])).cuda()
+eng.run_icp_batch(pool, counts, pairs, inits, epsilon=1e-3, normalize_error=True, return_correspondences=True)
+engine.nearest_batch(pool, counts, pairs[:2], return_dist2=True)
+engine.voxel_downsample_device(torch.from_numpy(src).cuda(), 0.01)
+rng = np.random.default_rng(0)
+p2, c2 = scans.scans_from_ranges(rng.uniform(0, 32, size=(9, 1081)), 0.1, 30.0)
+scans.statistical_outliers_removal_pool(p2, c2, 2)
+poses = synth.make_trajectories(1, 6, seed=2)[0]
+sp, sc = synth.cast_scans(poses, seed=2, device="cuda")
+m = ogm.OccupancyGridMap(0.05, 4.0, 3.0, -4.0, -3.0)          # small grid: rays leave it
+m.build_map(poses, (sp, sc))
+disp, rgb = to.synthetic_frames(2, 120, 160, seed=5)
+p = tm.TexturePainter(81, 61, 0.1, -4.0, -3.0, to.T_RC, to.K)
+p.paint_frames(disp, rgb, poses[:2])
+p.resolve(m.grid_map[:81, :61].copy())
+torch.cuda.synchronize()
+print("sanitize cases done")
