@@ -50,7 +50,9 @@ int b200icp_version(void);
 /* Human-readable text for a B200ICP_ERR_* code (static storage). */
 const char* b200icp_error_string(int code);
 
-/* Bytes of device workspace b200icp_run needs for this problem size. */
+/* Bytes of device workspace b200icp_run / b200icp_nearest need for this problem size: the work
+ * queue (256 B) and, for the general kernel (dim 3, or dim 2 with n_max > 2048), one fp32 copy of
+ * a target per resident cluster.  Concurrent launches need separate workspaces. */
 int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out);
 
 /* Batched point-to-point ICP.  Replaces, for every pair b independently,

@@ -1,5 +1,6 @@
 // extern "C" entry points of libb200icp.so (see include/b200icp.h).
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <stdlib.h>
 
 #include "icp2d.cuh"
@@ -10,6 +11,15 @@ using namespace b200icp;
 namespace {
 
 constexpr int kMax2d = 2048;  // 6-bit block id x 32 targets
+// General kernel: each resident cluster keeps an fp32 copy of its current target in the
+// workspace (read back by TMA).  At most this many clusters are launched (2 CTAs x 148 SMs).
+constexpr int kMaxClusterSlots = 296;
+
+inline bool uses_general_kernel(int n_max, int dim) { return !(dim == 2 && n_max <= kMax2d); }
+inline size_t tgt32_slot_floats(int n_max) {
+  const size_t np32 = (((size_t)n_max + 31) / 32) * 32;
+  return ((np32 * 3 + 31) / 32) * 32;          // 128-byte multiple
+}
 
 struct DeviceInfo {
   int sms;
@@ -41,7 +51,11 @@ int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
   return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
 }
 
-int launch3d(const RunParams& p, int dim, cudaStream_t stream, int sms) {
+int launch3d(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, int sms) {
+  const long long slots_needed = p.n_pairs < kMaxClusterSlots ? p.n_pairs : kMaxClusterSlots;
+  p.tgt32_stride = (long long)tgt32_slot_floats(p.n_max);
+  if (workspace_bytes < 256 + (size_t)slots_needed * p.tgt32_stride * sizeof(float)) return B200ICP_ERR_WORKSPACE;
+  p.tgt32 = reinterpret_cast<float*>(static_cast<char*>(workspace) + 256);
   constexpr int R = 4, TH = 256;
   auto kern = icp3d_kernel<R, TH>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
@@ -53,6 +67,10 @@ int launch3d(const RunParams& p, int dim, cudaStream_t stream, int sms) {
   const long long rows = ((long long)p.n_max + TH - 1) / TH;
   int g = 1;
   while (g < 16 && (long long)p.n_pairs * g < 8LL * sms && 4LL * g <= rows) g *= 2;
+  if (const char* e = getenv("B200ICP_CLUSTER_SIZE")) {     // tuning knob: 1, 2, 4, 8 or 16
+    const int v = atoi(e);
+    if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) g = v;
+  }
   for (; g >= 1; g /= 2) {
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute attr{};
@@ -66,7 +84,8 @@ int launch3d(const RunParams& p, int dim, cudaStream_t stream, int sms) {
       cudaGetLastError();
       continue;     // this cluster size cannot be co-scheduled: try a smaller one
     }
-    const long long want = p.n_pairs < clusters ? p.n_pairs : clusters;
+    long long want = p.n_pairs < clusters ? p.n_pairs : clusters;
+    if (want > kMaxClusterSlots) want = kMaxClusterSlots;
     cfg.gridDim = dim3((unsigned)(want * g));
     if (cudaLaunchKernelEx(&cfg, kern, p, dim) != cudaSuccess) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
     return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
@@ -94,7 +113,7 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     }
     return launch2d<8, 8, 2>(p, stream, d.sms);
   }
-  return launch3d(p, dim, stream, d.sms);
+  return launch3d(p, dim, workspace, workspace_bytes, stream, d.sms);
 }
 
 __global__ void ffma_probe_kernel(float* sink, int iters) {
@@ -146,7 +165,12 @@ const char* b200icp_error_string(int code) {
 
 int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out) {
   if (!bytes_out || n_pairs < 0 || n_max <= 0 || (dim != 2 && dim != 3)) return B200ICP_ERR_BAD_ARG;
-  *bytes_out = 256;  // the work-queue counter (padded)
+  size_t bytes = 256;  // the work-queue counter (padded)
+  if (uses_general_kernel(n_max, dim)) {
+    const size_t slots = (size_t)(n_pairs < kMaxClusterSlots ? n_pairs : kMaxClusterSlots);
+    bytes += slots * tgt32_slot_floats(n_max) * sizeof(float);   // fp32 target copies, one per resident cluster
+  }
+  *bytes_out = bytes;
   return B200ICP_OK;
 }
 

@@ -17,7 +17,7 @@
 
 namespace b200icp {
 
-constexpr int kTile3d = 2048;   // targets per shared-memory tile (fp32 [x4 y4 z4] groups: 24 KB)
+constexpr int kTile3d = 1536;   // targets per shared-memory tile (fp32 [x4 y4 z4] groups: 18 KB), two tiles in flight
 constexpr int kSums3d = 16;     // sum u(3) v(3) u v^T(9) sse
 constexpr int kRed3d = 22;      // + min/max per axis over moved source and matched target
 
@@ -64,10 +64,18 @@ __device__ __forceinline__ void sweep3d_block(const float* tile_blk, const f32x2
   }
 }
 
-// The sweep of one chunk (NR rows of TH source points) against the whole target: the target is
-// restaged tile by tile (fp64 -> fp32) by all threads of the CTA.  NR is CTA-uniform.
+// The sweep of one chunk (NR rows of TH source points) against the whole target.  The target's
+// fp32 copy (built once per pair in the workspace, already in tile layout) is streamed through
+// two shared-memory tiles with TMA bulk copies: thread 0 issues tile k+1 while the CTA sweeps
+// tile k; one mbarrier per tile signals arrival, one __syncthreads per tile frees it.
+struct TilePipe {
+  float* tile;          // [2][kTile3d * 3]
+  uint64_t* full;       // [2] mbarriers
+  uint32_t phase[2];
+};
+
 template <int NR, int R, int TH>
-__device__ __forceinline__ void sweep3d_chunk(float* tile, const double* tgt, int dim, int nt, int group,
+__device__ __forceinline__ void sweep3d_chunk(TilePipe& tp, const float* tgt32, int nt, int group,
                                               int nblk32, const float (&qx)[R], const float (&qy)[R],
                                               const float (&qz)[R], unsigned (&best)[R],
                                               unsigned (&second)[R]) {
@@ -79,19 +87,22 @@ __device__ __forceinline__ void sweep3d_chunk(float* tile, const double* tgt, in
     qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); qzz[r] = pack2(qz[r], qz[r]);
     bm[r] = __int_as_float(0x7f800000);
   }
-  for (int tbase = 0; tbase < nt; tbase += kTile3d) {
-    __syncthreads();
-    for (int i = tid; i < kTile3d; i += TH) {
-      float x = kBigCoord, y = kBigCoord, z = kBigCoord;
-      if (tbase + i < nt) {
-        double dx, dy, dz;
-        load_point(tgt, dim, tbase + i, dx, dy, dz);
-        x = (float)dx; y = (float)dy; z = (float)dz;
-      }
-      float* g = tile + (i >> 2) * 12 + (i & 3);
-      g[0] = x; g[4] = y; g[8] = z;
-    }
-    __syncthreads();
+  const int n_tiles = (nt + kTile3d - 1) / kTile3d;
+  auto issue = [&](int k) {
+    const int first = k * kTile3d;
+    const int blocks = (min(kTile3d, nt - first) + 31) >> 5;          // whole 32-target blocks (the copy is padded)
+    const uint32_t bytes = (uint32_t)blocks * 32u * 12u;
+    uint64_t* bar = tp.full + (k & 1);
+    mbar_expect_tx(bar, bytes);
+    tma_load_1d(tp.tile + (size_t)(k & 1) * kTile3d * 3, tgt32 + (size_t)first * 3, bytes, bar);
+  };
+  if (tid == 0) issue(0);
+  for (int k = 0; k < n_tiles; ++k) {
+    if (tid == 0 && k + 1 < n_tiles) issue(k + 1);                     // its buffer was freed by the barrier below
+    mbar_wait(tp.full + (k & 1), tp.phase[k & 1]);
+    tp.phase[k & 1] ^= 1u;
+    const float* tile = tp.tile + (size_t)(k & 1) * kTile3d * 3;
+    const int tbase = k * kTile3d;
     const int nb = (min(kTile3d, nt - tbase) + 31) >> 5;
     for (int b = 0; b < nb; ++b) {
       const int gb = (tbase >> 5) + b;
@@ -107,12 +118,14 @@ __device__ __forceinline__ void sweep3d_chunk(float* tile, const double* tgt, in
         }
       }
     }
+    __syncthreads();
   }
 }
 
 template <int R, int TH>
 __global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const int dim) {
-  __shared__ __align__(16) float tile[kTile3d * 3];     // groups of four targets: x4 y4 z4
+  __shared__ __align__(128) float tiles[2 * kTile3d * 3];  // two tiles of four-target groups: x4 y4 z4
+  __shared__ __align__(8) uint64_t full_bar[2];
   __shared__ double wpart[TH / 32][kRed3d];             // per-warp partial sums of this CTA
   __shared__ double part[2][kRed3d];                    // this CTA's sums, by pass parity (read by the cluster)
   __shared__ double s_tot[kRed3d];                      // cluster totals
@@ -122,6 +135,16 @@ __global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const i
   cg::cluster_group cluster = cg::this_cluster();
   const int G = (int)cluster.num_blocks();              // CTAs per pair
   const int rank = (int)cluster.block_rank();
+  TilePipe tp;
+  tp.tile = tiles; tp.full = full_bar; tp.phase[0] = tp.phase[1] = 0u;
+  if (threadIdx.x == 0) {
+    mbar_init(&full_bar[0], 1);
+    mbar_init(&full_bar[1], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  // this cluster's fp32 copy of the current target, in tile layout, padded to whole 32-target blocks
+  float* tgt32 = p.tgt32 + (size_t)(blockIdx.x / G) * p.tgt32_stride;
   const double kInf = __longlong_as_double(0x7ff0000000000000LL);
   constexpr float kTruncRel = 2.44140625e-4f;  // 2^-12 >= the 10 truncated mantissa bits (2^-13)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -195,6 +218,23 @@ __global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const i
     tmax *= (1.0f + 4.0f * kU);
     ox /= (double)nt; oy /= (double)nt; oz /= (double)nt;
     __syncthreads();
+    // ---- fp32 copy of the target (once per pair; each CTA converts a share, TMA reads it) ----
+    {
+      const int np32 = ((nt + 31) >> 5) << 5;
+      for (int i = rank * TH + tid; i < np32; i += G * TH) {
+        float x = kBigCoord, y = kBigCoord, z = kBigCoord;
+        if (i < nt) {
+          double dx, dy, dz;
+          load_point(tgt, dim, i, dx, dy, dz);
+          x = (float)dx; y = (float)dy; z = (float)dz;
+        }
+        float* g = tgt32 + (size_t)(i >> 2) * 12 + (i & 3);
+        g[0] = x; g[4] = y; g[8] = z;
+      }
+      __threadfence();
+      fence_proxy_async_global();     // generic-proxy stores -> visible to the TMA (async proxy) reads
+      cluster.sync();
+    }
 
     const double epsilon = p.nearest_only ? 0.0 : p.epsilon[pair];
     const bool normalize = p.nearest_only ? false : (p.normalize[pair] != 0);
@@ -237,48 +277,76 @@ __global__ void __launch_bounds__(TH, 2) icp3d_kernel(const RunParams p, const i
         }
         // ---- fp32 sweep, target streamed through the shared tile ----------------
         switch (nr) {
-          case 1: sweep3d_chunk<1, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
-          case 2: if constexpr (R >= 2) sweep3d_chunk<2, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
-          case 3: if constexpr (R >= 3) sweep3d_chunk<3, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
-          case 4: if constexpr (R >= 4) sweep3d_chunk<4, R, TH>(tile, tgt, dim, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 1: sweep3d_chunk<1, R, TH>(tp, tgt32, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 2: if constexpr (R >= 2) sweep3d_chunk<2, R, TH>(tp, tgt32, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 3: if constexpr (R >= 3) sweep3d_chunk<3, R, TH>(tp, tgt32, nt, group, nblk32, qx, qy, qz, best, second); break;
+          case 4: if constexpr (R >= 4) sweep3d_chunk<4, R, TH>(tp, tgt32, nt, group, nblk32, qx, qy, qz, best, second); break;
           default: break;
         }
         // ---- exact resolution ------------------------------------------------------
+        // Rescan of the best bookkeeping block: fp32 filter on the fp32 copy (L2), float64 on
+        // the few candidates that pass.  The R rows of a thread are walked together, group by
+        // group, so that their 3*R independent 16-byte loads are in flight at once.
         int corr[R];
-        unsigned ambiguous = 0;
+        unsigned ambiguous = 0, live = 0;
+        float thr[R];
+        int blo[R];
+        double px[R], py[R], pz[R], bd[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           const int j = cbase + tid + TH * r;
-          corr[r] = -1;
+          corr[r] = -1; thr[r] = 0.f; blo[r] = 0; bd[r] = kInf;
+          px[r] = py[r] = pz[r] = 0.0;
           if (r < nr && j < ns) {
             const int blk = (int)(best[r] & 1023u);
             const float bval = __uint_as_float(best[r] & 0xfffffc00u);
             const float sval = __uint_as_float(second[r] & 0xfffffc00u);
             const float a_bound = fmaxf(fabsf(qx[r]), fmaxf(fabsf(qy[r]), fabsf(qz[r]))) * (1.0f + 4.0f * kU) + tmax;
-            const float thr = candidate_threshold(bval, a_bound, kTruncRel);
-            if (!(sval > thr)) {
+            thr[r] = candidate_threshold(bval, a_bound, kTruncRel);
+            if (!(sval > thr[r])) {
               ambiguous |= 1u << r;
             } else {
-              double sx, sy, sz, x, y, z;
+              live |= 1u << r;
+              blo[r] = blk * bk_targets;
+              double sx, sy, sz;
               load_point(src, dim, j, sx, sy, sz);
-              T.apply(sx, sy, sz, x, y, z);
-              double bd = kInf;
-              int bi = -1;
-              const int lo = blk * bk_targets, hi = min(nt, lo + bk_targets);
-              for (int i = lo; i < hi; ++i) {
-                double ax, ay, az;
-                load_point(tgt, dim, i, ax, ay, az);
-                if (dist2_3d(qx[r], qy[r], qz[r], (float)ax, (float)ay, (float)az) <= thr) {
-                  const double ex = x - ax, ey = y - ay, ez = z - az;
-                  const double d = ex * ex + ey * ey + ez * ez;
-                  if (d < bd) { bd = d; bi = i; }
-                }
-              }
-              if (bi < 0) ambiguous |= 1u << r;
-              corr[r] = bi;
+              T.apply(sx, sy, sz, px[r], py[r], pz[r]);
             }
           }
         }
+        for (int off = 0; off < bk_targets; off += 4) {      // bk_targets is a multiple of 32
+          float4 X[R], Y[R], Z[R];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            // rows that are not live read group 0 of the copy (always present) and ignore it
+            const int i0 = ((live >> r) & 1u) ? min(blo[r] + off, ((nt - 1) >> 2) << 2) : 0;
+            const float4* g4 = reinterpret_cast<const float4*>(tgt32 + (size_t)(i0 >> 2) * 12);
+            X[r] = __ldcg(g4); Y[r] = __ldcg(g4 + 1); Z[r] = __ldcg(g4 + 2);
+          }
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            if (!((live >> r) & 1u)) continue;
+            const int i0 = blo[r] + off;
+            if (i0 >= nt) continue;
+            const float fxs[4] = {X[r].x, X[r].y, X[r].z, X[r].w};
+            const float fys[4] = {Y[r].x, Y[r].y, Y[r].z, Y[r].w};
+            const float fzs[4] = {Z[r].x, Z[r].y, Z[r].z, Z[r].w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int i = i0 + u;
+              if (i < nt && dist2_3d(qx[r], qy[r], qz[r], fxs[u], fys[u], fzs[u]) <= thr[r]) {
+                double ax, ay, az;
+                load_point(tgt, dim, i, ax, ay, az);
+                const double ex = px[r] - ax, ey = py[r] - ay, ez = pz[r] - az;
+                const double d = ex * ex + ey * ey + ez * ez;
+                if (d < bd[r]) { bd[r] = d; corr[r] = i; }
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (((live >> r) & 1u) && corr[r] < 0) ambiguous |= 1u << r;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           unsigned vote = __ballot_sync(0xffffffffu, (ambiguous >> r) & 1u);

@@ -156,6 +156,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+__device__ __forceinline__ void fence_proxy_async_global() {
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
 __device__ __forceinline__ void fence_mbar_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
@@ -210,6 +213,8 @@ struct RunParams {
   double* dist2_out;      // nearest-only mode
   int nearest_only;       // 1: single NN pass on untransformed queries, no solve
   unsigned int* queue;    // work counter in the workspace (zeroed before launch)
+  float* tgt32;           // general kernel: per-cluster fp32 copies of the current target (workspace)
+  long long tgt32_stride; // floats per cluster slot
   // fused pose exchange (multi-GPU): when n_peers > 0 the thread that finishes pair b also
   // stores its packed pose row (x, y, theta, error) into row peer_row0 + b of every rank's
   // gather buffer -- peer-mapped device pointers, i.e. plain stores that travel over NVLink.

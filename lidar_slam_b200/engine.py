@@ -140,7 +140,10 @@ def _copy_pool_pipelined(host_pool, dev_pool, pairs_host, dev, launch_chunk):
         st = comp_a if c % 2 == 0 else comp_b
         st.wait_event(ready)
         with torch.cuda.stream(st):
-            ws_c = torch.empty((256,), dtype=torch.uint8, device=dev)
+            nbytes = ctypes.c_size_t()
+            _lib.check(_lib.load().b200icp_workspace_bytes(hi - lo, dev_pool.shape[1], dev_pool.shape[2],
+                                                           ctypes.byref(nbytes)), "b200icp_workspace_bytes")
+            ws_c = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
             ws_c.record_stream(st)
             launch_chunk(lo, hi, ws_c)
     cur.wait_stream(copy_s)
@@ -248,7 +251,9 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
         # on a z-padded copy of the pool.
         scans3 = torch.zeros((n_scans, n_max, 3), dtype=torch.float64, device=dev)
         scans3[:, :, :2] = scans
-        launch(3, scans3, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
+        _lib.check(lib.b200icp_workspace_bytes(n_pairs, n_max, 3, ctypes.byref(nbytes)), "b200icp_workspace_bytes")
+        ws3 = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
+        launch(3, scans3, pairs, init, eps, norm, T, err, iters, status, corr, n_max, ws=ws3)
     else:
         launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
     return IcpBatchResult(T, err, iters, status, corr)
