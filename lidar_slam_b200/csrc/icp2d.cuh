@@ -33,7 +33,7 @@ constexpr int kRed2d = 17;    // + min/max of qx qy px py
 
 struct Smem2dLayout {
   int np;          // padded point capacity (multiple of 32)
-  size_t off_t64, off_s64, off_t32, off_red, off_ctl, total;
+  size_t off_t64, off_s64, off_t32, off_red, off_part, off_ctl, total;
 };
 __host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps) {
   Smem2dLayout L;
@@ -43,6 +43,7 @@ __host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps) {
   L.off_s64 = o; o += (size_t)L.np * 16;
   L.off_t32 = o; o += (size_t)L.np * 8;
   L.off_red = o; o += (size_t)2 * warps * kRed2d * 8;
+  L.off_part = o; o += (size_t)(warps - 1) * warps * 32 * 8;   // shared rows: (best, second) per warp and lane
   L.off_ctl = o; o += 64;
   L.total = o;
   return L;
@@ -60,14 +61,14 @@ __device__ __forceinline__ float2 target32(const float* t32, int i) {
 // Per 4 candidates: 2x(FADD2, FADD2, FMUL2, FFMA2) + 2 FMNMX3, i.e. 8 FP32-pipe issue slots
 // carrying the 16 algorithmic lane-instructions, plus 0.5 ALU slot per candidate.
 template <int NR, int RMAX>
-__device__ __forceinline__ void sweep2d(const float* t32, int nblk, const float (&qx)[RMAX],
+__device__ __forceinline__ void sweep2d(const float* t32, int blk_lo, int blk_hi, const float (&qx)[RMAX],
                                         const float (&qy)[RMAX], unsigned (&best)[RMAX],
                                         unsigned (&second)[RMAX]) {
   f32x2 qxx[NR], qyy[NR];
 #pragma unroll
   for (int r = 0; r < NR; ++r) { qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); }
   const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(t32);
-  for (int b = 0; b < nblk; ++b) {
+  for (int b = blk_lo; b < blk_hi; ++b) {
     float bm[NR];
 #pragma unroll
     for (int r = 0; r < NR; ++r) bm[r] = __int_as_float(0x7f800000);
@@ -104,6 +105,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
   double2* s64 = reinterpret_cast<double2*>(smem_raw + L.off_s64);
   float* t32 = reinterpret_cast<float*>(smem_raw + L.off_t32);
   double* red = reinterpret_cast<double*>(smem_raw + L.off_red);
+  uint2* part = reinterpret_cast<uint2*>(smem_raw + L.off_part);
   uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw + L.off_ctl);
   int* s_pair = reinterpret_cast<int*>(smem_raw + L.off_ctl + 16);
 
@@ -208,12 +210,17 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     const double epsilon = p.nearest_only ? 0.0 : p.epsilon[pair];
     const bool normalize = p.nearest_only ? false : (p.normalize[pair] != 0);
     const int nblk = (nt + kBlockTargets - 1) / kBlockTargets;
-    // rows of 32 source points are dealt out evenly: warp w owns rows [row0, row0 + nr)
+    // Rows of 32 source points.  Every warp owns `base` rows and sweeps them against all
+    // targets.  The rows % W rows left over are SHARED: every warp sweeps all of them against its
+    // 1/W of the target blocks, the per-warp (best, second) pairs meet in shared memory, and
+    // shared row e is then merged, resolved and summed by warp e (register slot `base`).  All
+    // warps therefore carry the same sweep load (34 rows on 8 warps: 4.25 each instead of 5/4).
     const int rows = (ns + 31) >> 5;
-    const int nr = rows / W + (warp < rows % W ? 1 : 0);
-    const int row0 = warp * (rows / W) + min(warp, rows % W);
-    const int wbase = row0 * 32;
-    const bool warp_active = nr > 0;
+    const int base = rows / W, extra = rows % W;
+    const int nr = base + (warp < extra ? 1 : 0);
+    const int n_shared_chunks = (extra + R - 1) / R;
+    const int sblk_lo = (warp * nblk) / W, sblk_hi = ((warp + 1) * nblk) / W;
+    auto row_of = [&](int r) { return r < base ? warp * base + r : base * W + warp; };
     StopState st{0.0, 0, 0};
     int passes = 0;
 
@@ -227,27 +234,30 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 #pragma unroll
       for (int r = 0; r < R; ++r) corr[r] = -1;
 
-      if (warp_active) {
-        // 1. transform
-        float qx[R], qy[R];
+      float qx[R], qy[R];
+      unsigned best[R], second[R];
+      // 1+2. transform and fp32 sweep: first the shared rows (chunks of <= R rows, this warp's
+      // share of the target blocks, results to shared memory), last this warp's own rows.
+      for (int ph = 0; ph <= n_shared_chunks; ++ph) {
+        const bool own = ph == n_shared_chunks;
+        const int cnt = own ? base : min(R, extra - ph * R);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const int j = wbase + lane + 32 * r;
+          const int row = own ? row_of(r) : base * W + ph * R + r;
+          const int j = row * 32 + lane;
           qx[r] = 0.f; qy[r] = 0.f;
-          if (r < nr && j < ns) {
+          best[r] = 0xffffffffu; second[r] = 0xffffffffu;
+          if (r < (own ? nr : cnt) && j < ns) {
             const double2 s = s64[j];
             qx[r] = (float)fma(r00, s.x, fma(r01, s.y, tx));
             qy[r] = (float)fma(r10, s.x, fma(r11, s.y, ty));
           }
         }
-        // 2. fp32 sweep with per-block (value | block id) top-2 tracking
-        unsigned best[R], second[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) { best[r] = 0xffffffffu; second[r] = 0xffffffffu; }
-        switch (nr) {
+        const int blk_lo = own ? 0 : sblk_lo, blk_hi = own ? nblk : sblk_hi;
+        switch (cnt) {
 #define B200ICP_SWEEP_CASE(N) \
   case N:                     \
-    if constexpr (N <= R) sweep2d<N, R>(t32, nblk, qx, qy, best, second); \
+    if constexpr (N <= R) sweep2d<N, R>(t32, blk_lo, blk_hi, qx, qy, best, second); \
     break;
           B200ICP_SWEEP_CASE(1) B200ICP_SWEEP_CASE(2) B200ICP_SWEEP_CASE(3) B200ICP_SWEEP_CASE(4)
           B200ICP_SWEEP_CASE(5) B200ICP_SWEEP_CASE(6) B200ICP_SWEEP_CASE(7) B200ICP_SWEEP_CASE(8)
@@ -255,11 +265,33 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 #undef B200ICP_SWEEP_CASE
           default: break;
         }
+        if (!own) {
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            if (r < cnt) part[((ph * R + r) * W + warp) * 32 + lane] = make_uint2(best[r], second[r]);
+        }
+      }
+      if (extra > 0) {
+        __syncthreads();        // the shared rows' partial results are complete
+        if (warp < extra) {     // merge the W partial top-2 lists of shared row `warp` into slot `base`
+          unsigned b = 0xffffffffu, s2 = 0xffffffffu;
+#pragma unroll
+          for (int w = 0; w < W; ++w) {
+            const uint2 o = part[(warp * W + w) * 32 + lane];
+            s2 = min(min(s2, o.y), max(b, o.x));
+            b = min(b, o.x);
+          }
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            if (r == base) { best[r] = b; second[r] = s2; }
+        }
+      }
+      if (nr > 0) {
         // 3. exact resolution in float64
         unsigned ambiguous = 0;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const int j = wbase + lane + 32 * r;
+          const int j = row_of(r) * 32 + lane;
           if (r < nr && j < ns) {
             const int blk = (int)(best[r] & 63u);
             const float bval = __uint_as_float(best[r] & 0xffffffc0u);
@@ -312,7 +344,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
             const unsigned bpk = __shfl_sync(0xffffffffu, best[r], src_lane);
             const float a_bound = fmaxf(fabsf(fx), fabsf(fy)) * (1.0f + 4.0f * kU) + tmax;
             const float thr = candidate_threshold(__uint_as_float(bpk & 0xffffffc0u), a_bound, kTruncRel);
-            const int j = wbase + src_lane + 32 * r;
+            const int j = row_of(r) * 32 + src_lane;
             const double2 s = s64[j];
             const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
             const double qdy = fma(r10, s.x, fma(r11, s.y, ty));
@@ -335,7 +367,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         // 4. float64 sums over this thread's matched pairs
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const int j = wbase + lane + 32 * r;
+          const int j = row_of(r) * 32 + lane;
           if (r < nr && j < ns) {
             const double2 s = s64[j];
             const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
@@ -455,7 +487,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           int* out = p.corr_out + (size_t)pair * p.n_max;
 #pragma unroll
           for (int r = 0; r < R; ++r) {
-            const int j = wbase + lane + 32 * r;
+            const int j = row_of(r) * 32 + lane;
             if (r < nr && j < ns) out[j] = corr[r];
           }
           for (int j = ns + tid; j < p.n_max; j += W * 32) out[j] = -1;
