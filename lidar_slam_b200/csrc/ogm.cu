@@ -1,42 +1,45 @@
 // Occupancy-grid ray casting on the device: the consumer of the
 // poses the ICP path produces.
 //
-//   ogm_build_kernel   OccupancyGridMap.update_map / build_map   modules/ogm.py:149-195, :46-60
-//                      OccupancyGridMap.bresenham2D              modules/ogm.py:197-231
-//                      OccupancyGridMap.world2grid               modules/ogm.py:104-126
-//   ogm_binarize       the pmf thresholding of build_map         modules/ogm.py:62-65
+//   ogm_count/classify/event/apply   OccupancyGridMap.update_map / build_map   modules/ogm.py:149-195, :46-60
+//                                    OccupancyGridMap.bresenham2D              modules/ogm.py:197-231
+//                                    OccupancyGridMap.world2grid               modules/ogm.py:104-126
+//   ogm_binarize                     the pmf thresholding of build_map         modules/ogm.py:62-65
 //
 // The reference updates a float32 log-odds grid one ray after another:
 //     cell -= log 4  for every in-bounds cell of the ray but the last,  cell += log 4 for the last,
 // each update being  f32(f64(cell) -/+ log 4)  (numpy in-place op with a float64 scalar), and
-// clips the grid to [-20, 20] after every scan.  Rounding makes the result depend on the ORDER
-// of the updates a cell receives, so the kernel reproduces that order exactly:
-//   phase 1  all rays of the scan are walked in parallel (one thread per ray; the in-bounds part
-//            of a ray is entered through the closed form of the reference's Bresenham variant);
-//            every visited cell gets its decrement / increment COUNT with a fire-and-forget
-//            atomic on an int32 scratch grid;
-//   phase 2  the scan's bounding window of the scratch grid is swept: a cell that only saw
-//            decrements (or only increments) replays that many rounded updates -- the order
-//            among identical updates is immaterial; a cell that saw both is queued;
-//   phase 3  rays are walked again and append (ray, sign) events to the queued cells, each
-//            cell then sorts its events by ray index and replays them in the reference's order.
-// Scans are order-dependent (clip + rounding), so one map is a sequential chain of scans.  A
-// thread-block CLUSTER of 16 CTAs (16 SMs) owns one map: the per-scan work is spread over the
-// cluster's threads (the count atomics are bound by the per-SM atomic issue rate, so SMs are
-// what it needs) and the phases are separated by hardware cluster barriers instead of kernel
-// launches.  Several maps (odometry / scan-matching / optimised trajectories) run side by
-// side, one cluster each.
-#include <cooperative_groups.h>
+// clips the grid to [-20, 20] after every scan.  Rounding and clipping make the value of a cell
+// depend on the ORDER of the updates it receives -- but only on the updates of THAT cell.  So
+// the chain "scan after scan, ray after ray" is kept per cell and everything else runs in
+// parallel over the whole GPU, a BATCH of up to 64 scans (of every map) at a time:
+//   count     one thread per ray of every scan of the batch (the in-bounds part of a ray is
+//             entered through the closed form of the reference's Bresenham variant); every
+//             visited cell gets its decrement / increment COUNT with a fire-and-forget atomic on
+//             the int32 count plane of its scan;
+//   classify  the bounding window of every scan's plane is swept; a (scan, cell) that saw both
+//             decrements and increments is given an event list;
+//   event     the rays are walked again and append (ray, sign) to the tagged cells;
+//   apply     one thread per cell walks the batch scan by scan: single-sign counts replay that
+//             many rounded updates (the order among identical updates is immaterial), tagged
+//             entries sort their events by ray index and replay them in the reference's order;
+//             clip after every scan; the planes are left zeroed for the next batch.
+// Event storage is sized for the usual case; an entry that does not fit is replayed by testing
+// every ray of its scan against the cell with the closed form (slow, exact, rare).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/b200icp.h"
 
 namespace {
 
-constexpr int kThreads = 256;     // per CTA
-constexpr int kCluster = 16;      // CTAs (= SMs) that share one map; opt-in cluster size on sm_100
-constexpr int kMixedCap = 16384;
+constexpr int kThreads = 256;
+constexpr int kBatchMax = 64;                     // scans per batch (count planes per map)
+constexpr size_t kPlaneBudget = (size_t)96 << 20; // bytes of count planes per map that set the batch size
+constexpr int kSlotsPerScan = 4096;               // event lists per scan of the batch (average)
+constexpr int kEventsPerRay = 16;                 // event capacity per ray of the batch (average)
+constexpr unsigned kOverflowTag = 0xffffffffu;
 constexpr double kLogOdds = 1.3862943611198906;   // np.log(4.)  (modules/ogm.py:44)
 constexpr int kSaturate = 30;                     // 30 * log 4 = 41.6 > 40 = the width of the clip interval
 
@@ -49,9 +52,16 @@ struct OgmParams {
   const double* scans;    // [n_scans][n_max][2] shared by all maps
   const int32_t* counts;  // [n_scans]
   int n_scans, n_max, n_maps;
-  int32_t* workspace;     // per map: scratch[w*h] | ctl[16] | mixed_cell/cnt/off/fill[cap] | events[ev_cap]
-  long long ws_stride;    // int32 elements per map
-  int ev_cap;
+  int s0, sb;             // this batch: scans [s0, s0 + sb)
+  int batch;              // planes per map (capacity)
+  int32_t* planes;        // [n_maps][batch][width*height]  dec count | inc count << 16, or tag
+  int32_t* bbox;          // [n_maps][batch][4]  min x, min -x, min y, min -y of the visited window
+  int32_t* ctl;           // [n_maps][4]  event lists used, events used
+  int32_t* slot_cnt;      // [n_maps][slot_cap]
+  int32_t* slot_off;      // [n_maps][slot_cap]
+  int32_t* slot_fill;     // [n_maps][slot_cap]
+  int32_t* events;        // [n_maps][ev_cap]
+  int slot_cap, ev_cap;
 };
 
 // modules/ogm.py:104-126: ceil((x - min)/res) - 1 (float64 arithmetic, then integer)
@@ -128,186 +138,261 @@ __device__ __forceinline__ float apply_updates(float a, int n, double delta) {
 }
 __device__ __forceinline__ float clip20(float a) { return fminf(fmaxf(a, -20.0f), 20.0f); }
 
-// Walk every ray of the scan: MODE 0 counts visits on the scratch grid, MODE 1 appends
-// (ray, sign) events to the queued (tagged) cells.
+
+// Pose-dependent data of one scan of one map.
+struct ScanFrame {
+  double x, y, c, sn;
+  int sx, sy;        // start cell: pose + lidar offset, NOT rotated (modules/ogm.py:165-166)
+  int n_rays;
+};
+
+__device__ __forceinline__ ScanFrame scan_frame(const OgmParams& p, int map, int s) {
+  ScanFrame f;
+  const double* pose = p.poses + ((size_t)map * p.n_scans + s) * 3;
+  const double* cs = p.cs + ((size_t)map * p.n_scans + s) * 2;
+  f.x = pose[0]; f.y = pose[1]; f.c = cs[0]; f.sn = cs[1];
+  f.sx = world2grid(__dadd_rn(f.x, 0.13323), p.min_x, p.res);
+  f.sy = world2grid(__dadd_rn(f.y, 0.0), p.min_y, p.res);
+  f.n_rays = min(p.counts[s], p.n_max);
+  return f;
+}
+
+// End cell of ray i: the end point to the world frame (modules/ogm.py:160-162:
+// np.dot(z_t, R_wr.T) + [x, y], row . column with R = [[c, -s], [s, c]]) and to cells (:170).
+__device__ __forceinline__ int2 ray_end(const OgmParams& p, const ScanFrame& f, int s, int i) {
+  const double2 q = reinterpret_cast<const double2*>(p.scans + (size_t)s * p.n_max * 2)[i];
+  const double wx = __dadd_rn(__dadd_rn(__dmul_rn(q.x, f.c), __dmul_rn(q.y, -f.sn)), f.x);
+  const double wy = __dadd_rn(__dadd_rn(__dmul_rn(q.x, f.sn), __dmul_rn(q.y, f.c)), f.y);
+  return make_int2(world2grid(wx, p.min_x, p.res), world2grid(wy, p.min_y, p.res));
+}
+
+// Walk one ray, classic incremental stepping (rem is the numerator of the closed form modulo
+// dx, m its quotient).  MODE 0 counts visits on the plane, MODE 1 appends (ray, sign) events to
+// the tagged cells.
 template <int MODE>
-__device__ __forceinline__ void walk_rays(const int2* ends, int n_rays, int sx, int sy, int width,
-                                          int height, int32_t* scratch, const int32_t* mixed_off,
-                                          int32_t* mixed_fill, int32_t* events, int gtid, int gthreads) {
-  // one thread per ray, classic incremental stepping: rem is the numerator of the closed form
-  // modulo dx, m its quotient
-  for (int ray = gtid; ray < n_rays; ray += gthreads) {
-    const int2 e = ends[ray];
-    const Ray r = make_ray(sx, sy, e.x, e.y, width, height);
-    if (r.klo > r.khi) continue;
-    const int dx = r.dx, dy = r.dy;
-    int m = 0, rem = r.c0;
-    if (r.klo > 0) {
-      const unsigned num = (unsigned)r.klo * (unsigned)dy + (unsigned)r.c0;
-      m = (int)(num / (unsigned)dx);
-      rem = (int)(num - (unsigned)m * (unsigned)dx);
+__device__ __forceinline__ void walk_ray(const Ray& r, int ray, int height, int32_t* plane,
+                                         const int32_t* slot_off, int32_t* slot_fill, int32_t* events) {
+  if (r.klo > r.khi) return;
+  const int dx = r.dx, dy = r.dy;
+  int m = 0, rem = r.c0;
+  if (r.klo > 0) {
+    const unsigned num = (unsigned)r.klo * (unsigned)dy + (unsigned)r.c0;
+    m = (int)(num / (unsigned)dx);
+    rem = (int)(num - (unsigned)m * (unsigned)dx);
+  }
+  // the cell index advances by a fixed stride per major step and another per minor step
+  const int smaj = r.steep ? (r.sy <= r.ey ? 1 : -1) : (r.sx <= r.ex ? height : -height);
+  const int smin = r.steep ? (r.sx <= r.ex ? height : -height) : (r.sy <= r.ey ? 1 : -1);
+  int cell = r.sx * height + r.sy + r.klo * smaj + m * smin;
+  if (MODE == 0) {
+    for (int k = r.klo; k <= r.khi; ++k) {
+      atomicAdd(&plane[cell], k == r.khi ? 0x10000 : 1);
+      rem += dy;
+      cell += smaj;
+      if (rem >= dx && dx > 0) { rem -= dx; cell += smin; }
     }
-    // cell index advances by a fixed stride per major step and another per minor step
-    const int smaj = r.steep ? (r.sy <= r.ey ? 1 : -1) : (r.sx <= r.ex ? height : -height);
-    const int smin = r.steep ? (r.sx <= r.ex ? height : -height) : (r.sy <= r.ey ? 1 : -1);
-    int cell = sx * height + sy + r.klo * smaj + m * smin;
-    if (MODE == 0) {
-      for (int k = r.klo; k <= r.khi; ++k) {
-        atomicAdd(&scratch[cell], k == r.khi ? 0x10000 : 1);
+  } else {
+    // the tag loads are independent of one another: issue eight before looking at any
+    constexpr int U = 8;
+    for (int k0 = r.klo; k0 <= r.khi; k0 += U) {
+      int tags[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        tags[u] = (k0 + u <= r.khi) ? __ldcg(&plane[cell]) : 0;
         rem += dy;
         cell += smaj;
         if (rem >= dx && dx > 0) { rem -= dx; cell += smin; }
       }
-    } else {
-      // the tag loads are independent of one another: issue eight before looking at any
-      constexpr int U = 8;
-      for (int k0 = r.klo; k0 <= r.khi; k0 += U) {
-        int cells[U], tags[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          cells[u] = cell;
-          tags[u] = (k0 + u <= r.khi) ? __ldcg(&scratch[cell]) : 0;
-          rem += dy;
-          cell += smaj;
-          if (rem >= dx && dx > 0) { rem -= dx; cell += smin; }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (tags[u] < 0) {
-            const int slot = tags[u] & 0x7fffffff;
-            const int pos = atomicAdd(&mixed_fill[slot], 1);
-            events[mixed_off[slot] + pos] = (ray << 1) | ((k0 + u == r.khi) ? 1 : 0);
-          }
+      for (int u = 0; u < U; ++u) {
+        if (tags[u] < 0 && (unsigned)tags[u] != kOverflowTag) {
+          const int slot = tags[u] & 0x7fffffff;
+          const int pos = atomicAdd(&slot_fill[slot], 1);
+          events[slot_off[slot] + pos] = (ray << 1) | ((k0 + u == r.khi) ? 1 : 0);
         }
       }
     }
   }
 }
 
-#ifdef B200ICP_OGM_PROFILE
-__device__ __forceinline__ long long gtime() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define PH(i) do { const long long now_ = gtime(); ph[i] += now_ - t_last; t_last = now_; } while (0)
-#else
-#define PH(i) do { } while (0)
-#endif
+// Does ray r visit cell (cx, cy) (a cell inside the grid)?  Returns 0 (no), -1 (decrement) or
+// +1 (increment: the last in-bounds cell of the ray).  Closed form of the walk above.
+__device__ __forceinline__ int ray_visit(const Ray& r, int cx, int cy) {
+  if (r.klo > r.khi) return 0;
+  const int k = r.steep ? (r.sy <= r.ey ? cy - r.sy : r.sy - cy) : (r.sx <= r.ex ? cx - r.sx : r.sx - cx);
+  if (k < r.klo || k > r.khi) return 0;
+  const int m = r.dx > 0 ? (int)(((unsigned)k * (unsigned)r.dy + (unsigned)r.c0) / (unsigned)r.dx) : 0;
+  const int minor = r.steep ? r.sx + (r.sx <= r.ex ? m : -m) : r.sy + (r.sy <= r.ey ? m : -m);
+  if (minor != (r.steep ? cx : cy)) return 0;
+  return k == r.khi ? 1 : -1;
+}
 
-__global__ void __launch_bounds__(kThreads, 1) ogm_build_kernel(const OgmParams p) {
-#ifdef B200ICP_OGM_PROFILE
-  long long ph[6] = {0, 0, 0, 0, 0, 0};
-  long long t_last = gtime();
-#endif
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  int2* ends = reinterpret_cast<int2*>(smem_raw);                  // [n_max] end cells of the rays
-  __shared__ int s_bbox[4];
-  namespace cg = cooperative_groups;
-  cg::cluster_group cluster = cg::this_cluster();
-  const int map = blockIdx.x / kCluster;
-  const int tid = threadIdx.x;
-  const int gtid = (int)cluster.block_rank() * kThreads + tid;      // thread index within the cluster
-  constexpr int gthreads = kCluster * kThreads;
-  float* grid = p.log_odds + (size_t)map * p.width * p.height;
-  int32_t* ws = p.workspace + (size_t)map * p.ws_stride;
-  int32_t* scratch = ws;
-  int32_t* ctl = ws + (size_t)p.width * p.height;                  // [0] n_mixed, [1] ev_total, [2] again
-  int32_t* mixed_cell = ctl + 16;
-  int32_t* mixed_cnt = mixed_cell + kMixedCap;
-  int32_t* mixed_off = mixed_cnt + kMixedCap;
-  int32_t* mixed_fill = mixed_off + kMixedCap;
-  int32_t* events = mixed_fill + kMixedCap;
-  const int W = p.width, H = p.height;
+__global__ void ogm_reset_kernel(const OgmParams p) {
+  const int n_bbox = p.n_maps * p.batch * 4, n_ctl = p.n_maps * 4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_bbox + n_ctl; i += gridDim.x * blockDim.x) {
+    if (i < n_bbox) p.bbox[i] = 0x7fffffff;
+    else p.ctl[i - n_bbox] = 0;
+  }
+}
 
-  for (int s = 0; s < p.n_scans; ++s) {
-    const double* pose = p.poses + ((size_t)map * p.n_scans + s) * 3;
-    const double* cs = p.cs + ((size_t)map * p.n_scans + s) * 2;
-    const double x = pose[0], y = pose[1], c = cs[0], sn = cs[1];
-    const int n_rays = min(p.counts[s], p.n_max);
-    // ray start: pose + lidar offset, NOT rotated (modules/ogm.py:165-166)
-    const int sx = world2grid(__dadd_rn(x, 0.13323), p.min_x, p.res);
-    const int sy = world2grid(__dadd_rn(y, 0.0), p.min_y, p.res);
-    if (tid == 0) { s_bbox[0] = sx; s_bbox[1] = sx; s_bbox[2] = sy; s_bbox[3] = sy; }
-    __syncthreads();
-    // end points to the world frame (modules/ogm.py:160-162) and to cells (:170)
-    const double2* z = reinterpret_cast<const double2*>(p.scans + (size_t)s * p.n_max * 2);
-    int bx0 = sx, bx1 = sx, by0 = sy, by1 = sy;
-    for (int i = tid; i < n_rays; i += kThreads) {
-      const double2 q = z[i];
-      // np.dot(z_t, R_wr.T) + [x, y]: row . column with R = [[c, -s], [s, c]]
-      const double wx = __dadd_rn(__dadd_rn(__dmul_rn(q.x, c), __dmul_rn(q.y, -sn)), x);
-      const double wy = __dadd_rn(__dadd_rn(__dmul_rn(q.x, sn), __dmul_rn(q.y, c)), y);
-      const int ex = world2grid(wx, p.min_x, p.res), ey = world2grid(wy, p.min_y, p.res);
-      ends[i] = make_int2(ex, ey);
-      bx0 = min(bx0, ex); bx1 = max(bx1, ex); by0 = min(by0, ey); by1 = max(by1, ey);
+__device__ __forceinline__ int warp_min_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// count: grid (ray blocks, scans of the batch, maps)
+__global__ void __launch_bounds__(kThreads) ogm_count_kernel(const OgmParams p) {
+  const int sl = blockIdx.y, map = blockIdx.z, s = p.s0 + sl;
+  const ScanFrame f = scan_frame(p, map, s);
+  if (blockIdx.x * kThreads >= max(f.n_rays, 1)) return;
+  const size_t cells = (size_t)p.width * p.height;
+  int32_t* plane = p.planes + ((size_t)map * p.batch + sl) * cells;
+  const int ray = blockIdx.x * kThreads + threadIdx.x;
+  // window of the scan: start cell and every end cell (a Bresenham line stays inside the box of
+  // its two ends); kept as minima of x, -x, y, -y
+  int b0 = f.sx, b1 = -f.sx, b2 = f.sy, b3 = -f.sy;
+  if (ray < f.n_rays) {
+    const int2 e = ray_end(p, f, s, ray);
+    b0 = min(b0, e.x); b1 = min(b1, -e.x); b2 = min(b2, e.y); b3 = min(b3, -e.y);
+    const Ray r = make_ray(f.sx, f.sy, e.x, e.y, p.width, p.height);
+    walk_ray<0>(r, ray, p.height, plane, nullptr, nullptr, nullptr);
+  }
+  b0 = warp_min_i(b0); b1 = warp_min_i(b1); b2 = warp_min_i(b2); b3 = warp_min_i(b3);
+  if ((threadIdx.x & 31) == 0) {
+    int32_t* bb = p.bbox + ((size_t)map * p.batch + sl) * 4;
+    atomicMin(&bb[0], b0); atomicMin(&bb[1], b1); atomicMin(&bb[2], b2); atomicMin(&bb[3], b3);
+  }
+}
+
+struct Window { int x0, x1, y0, y1; };
+__device__ __forceinline__ Window scan_window(const OgmParams& p, int map, int sl) {
+  const int32_t* bb = p.bbox + ((size_t)map * p.batch + sl) * 4;
+  Window w;
+  w.x0 = max(bb[0], 0); w.x1 = min(-bb[1], p.width - 1);
+  w.y0 = max(bb[2], 0); w.y1 = min(-bb[3], p.height - 1);
+  return w;
+}
+
+// classify: grid (cell blocks, scans of the batch, maps)
+__global__ void __launch_bounds__(kThreads) ogm_classify_kernel(const OgmParams p) {
+  const int sl = blockIdx.y, map = blockIdx.z;
+  const Window w = scan_window(p, map, sl);
+  const int wh = w.y1 - w.y0 + 1, ww = w.x1 - w.x0 + 1;
+  if (wh <= 0 || ww <= 0) return;
+  const int wcells = ww * wh;
+  const size_t cells = (size_t)p.width * p.height;
+  int32_t* plane = p.planes + ((size_t)map * p.batch + sl) * cells;
+  int32_t* ctl = p.ctl + map * 4;
+  int32_t* cnt = p.slot_cnt + (size_t)map * p.slot_cap;
+  int32_t* off = p.slot_off + (size_t)map * p.slot_cap;
+  int32_t* fill = p.slot_fill + (size_t)map * p.slot_cap;
+  for (int t = blockIdx.x * kThreads + threadIdx.x; t < wcells; t += gridDim.x * kThreads) {
+    const int cell = (w.x0 + t / wh) * p.height + w.y0 + t % wh;
+    const int v = __ldcg(&plane[cell]);
+    const int dec = v & 0xffff, inc = (v >> 16) & 0x7fff;
+    if (dec == 0 || inc == 0) continue;
+    const int n = dec + inc;
+    unsigned tag = kOverflowTag;
+    const int o = atomicAdd(&ctl[1], n);
+    if (o + n <= p.ev_cap) {
+      const int slot = atomicAdd(&ctl[0], 1);
+      if (slot < p.slot_cap) {
+        cnt[slot] = n; off[slot] = o; fill[slot] = 0;
+        tag = 0x80000000u | (unsigned)slot;
+      }
     }
-    atomicMin(&s_bbox[0], bx0); atomicMax(&s_bbox[1], bx1);
-    atomicMin(&s_bbox[2], by0); atomicMax(&s_bbox[3], by1);
-    __syncthreads();
-    PH(0);
-    // ---- phase 1: visit counts --------------------------------------------------------
-    walk_rays<0>(ends, n_rays, sx, sy, W, H, scratch, nullptr, nullptr, nullptr, gtid, gthreads);
-    __threadfence();
-    cluster.sync();
-    PH(1);
-    const int wx0 = max(s_bbox[0], 0), wx1 = min(s_bbox[1], W - 1);
-    const int wy0 = max(s_bbox[2], 0), wy1 = min(s_bbox[3], H - 1);
-    const int wh = wy1 - wy0 + 1, ww = wx1 - wx0 + 1;
-    const long long wcells = (ww > 0 && wh > 0) ? (long long)ww * wh : 0;
-    for (;;) {
-      if (gtid == 0) { ctl[0] = 0; ctl[1] = 0; ctl[2] = 0; }
-      __threadfence();
-      cluster.sync();
-      // ---- phase 2: replay single-sign cells, queue mixed ones -------------------------
-      auto handle = [&](int cell, int v) {
-        if (v == 0) return;
-        const int dec = v & 0xffff, inc = (v >> 16) & 0x7fff;
-        if (dec == 0 || inc == 0) {
-          float a = __ldcg(&grid[cell]);
-          // the grid enters a scan inside [-20, 20] and every update moves by log 4 (up to an ulp):
-          // after 30 same-sign updates the value is beyond the clip whatever it started from
+    plane[cell] = (int)tag;
+  }
+}
+
+// event: same grid as count
+__global__ void __launch_bounds__(kThreads) ogm_event_kernel(const OgmParams p) {
+  const int sl = blockIdx.y, map = blockIdx.z, s = p.s0 + sl;
+  if (__ldcg(&p.ctl[map * 4]) == 0) return;          // no event list in this batch
+  const ScanFrame f = scan_frame(p, map, s);
+  const int ray = blockIdx.x * kThreads + threadIdx.x;
+  if (ray >= f.n_rays) return;
+  const size_t cells = (size_t)p.width * p.height;
+  int32_t* plane = p.planes + ((size_t)map * p.batch + sl) * cells;
+  const int2 e = ray_end(p, f, s, ray);
+  const Ray r = make_ray(f.sx, f.sy, e.x, e.y, p.width, p.height);
+  walk_ray<1>(r, ray, p.height, plane, p.slot_off + (size_t)map * p.slot_cap,
+              p.slot_fill + (size_t)map * p.slot_cap, p.events + (size_t)map * p.ev_cap);
+}
+
+// apply: grid (cell blocks, 1, maps); one thread per cell of the union of the batch's windows
+__global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) {
+  __shared__ Window win[kBatchMax];
+  __shared__ int uni[4];
+  const int map = blockIdx.z, tid = threadIdx.x;
+  if (tid == 0) { uni[0] = 0x7fffffff; uni[1] = -1; uni[2] = 0x7fffffff; uni[3] = -1; }
+  __syncthreads();
+  if (tid < p.sb) {
+    const Window w = scan_window(p, map, tid);
+    win[tid] = w;
+    if (w.x0 <= w.x1 && w.y0 <= w.y1) {
+      atomicMin(&uni[0], w.x0); atomicMax(&uni[1], w.x1);
+      atomicMin(&uni[2], w.y0); atomicMax(&uni[3], w.y1);
+    }
+  }
+  __syncthreads();
+  const int ux0 = uni[0], ux1 = uni[1], uy0 = uni[2], uy1 = uni[3];
+  const int uh = uy1 - uy0 + 1, uw = ux1 - ux0 + 1;
+  if (uh <= 0 || uw <= 0) return;
+  const int ucells = uw * uh;
+  const size_t cells = (size_t)p.width * p.height;
+  float* grid = p.log_odds + (size_t)map * cells;
+  int32_t* planes = p.planes + (size_t)map * p.batch * cells;
+  const int32_t* cnt = p.slot_cnt + (size_t)map * p.slot_cap;
+  const int32_t* off = p.slot_off + (size_t)map * p.slot_cap;
+  int32_t* events = p.events + (size_t)map * p.ev_cap;
+
+  for (int t = blockIdx.x * kThreads + tid; t < ucells; t += gridDim.x * kThreads) {
+    const int cx = ux0 + t / uh, cy = uy0 + t % uh;
+    const int cell = cx * p.height + cy;
+    float a = 0.f;
+    bool loaded = false;
+    for (int s8 = 0; s8 < p.sb; s8 += 8) {
+      int v[8];
+      int any = 0;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        v[u] = 0;
+        const int sl = s8 + u;
+        if (sl < p.sb) {
+          const Window w = win[sl];
+          if (cx >= w.x0 && cx <= w.x1 && cy >= w.y0 && cy <= w.y1) v[u] = __ldcg(&planes[(size_t)sl * cells + cell]);
+        }
+        any |= v[u];
+      }
+      if (!any) continue;
+      if (!loaded) { a = __ldcg(&grid[cell]); loaded = true; }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (v[u] == 0) continue;
+        const int sl = s8 + u;
+        if (v[u] > 0) {
+          // only decrements or only increments.  The cell enters a scan inside [-20, 20] and every
+          // update moves by log 4 (up to an ulp): after 30 same-sign updates the value is beyond
+          // the clip whatever it started from
+          const int dec = v[u] & 0xffff, inc = (v[u] >> 16) & 0x7fff;
           if (dec >= kSaturate) a = -20.0f;
           else if (inc >= kSaturate) a = 20.0f;
           else a = dec ? apply_updates(a, dec, -kLogOdds) : apply_updates(a, inc, kLogOdds);
-          grid[cell] = clip20(a);                                   // modules/ogm.py:191
-          scratch[cell] = 0;
-        } else {
-          const int n = dec + inc;
-          const int off = atomicAdd(&ctl[1], n);
-          if (off + n > p.ev_cap) { ctl[2] = 1; return; }
-          const int slot = atomicAdd(&ctl[0], 1);
-          if (slot >= kMixedCap) { ctl[2] = 1; return; }
-          mixed_cell[slot] = cell; mixed_cnt[slot] = n; mixed_off[slot] = off; mixed_fill[slot] = 0;
-          scratch[cell] = (int)(0x80000000u | (unsigned)slot);
-        }
-      };
-      // four independent loads in flight per thread (the sweep is latency-bound otherwise)
-      for (int t0 = gtid; t0 < (int)wcells; t0 += 4 * gthreads) {
-        int cell[4], v[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int t = t0 + u * gthreads;
-          cell[u] = -1; v[u] = 0;
-          if (t < (int)wcells) {
-            cell[u] = (wx0 + t / wh) * H + wy0 + t % wh;
-            v[u] = __ldcg(&scratch[cell[u]]);
+        } else if ((unsigned)v[u] == kOverflowTag) {
+          // no room for an event list: test every ray of the scan against this cell, in ray order
+          const int s = p.s0 + sl;
+          const ScanFrame f = scan_frame(p, map, s);
+          for (int i = 0; i < f.n_rays; ++i) {
+            const int2 e = ray_end(p, f, s, i);
+            const int hit = ray_visit(make_ray(f.sx, f.sy, e.x, e.y, p.width, p.height), cx, cy);
+            if (hit) a = apply_updates(a, 1, hit > 0 ? kLogOdds : -kLogOdds);
           }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) handle(cell[u], v[u]);
-      }
-      __threadfence();
-      cluster.sync();
-      PH(2);
-      const int n_mixed = min(__ldcg(&ctl[0]), kMixedCap);
-      if (n_mixed > 0) {
-        // ---- phase 3: ordered replay of the mixed cells -------------------------------
-        walk_rays<1>(ends, n_rays, sx, sy, W, H, scratch, mixed_off, mixed_fill, events, gtid, gthreads);
-        __threadfence();
-        cluster.sync();
-        PH(3);
-        for (int slot = gtid; slot < n_mixed; slot += gthreads) {
-          const int32_t* ev = events + mixed_off[slot];
-          const int n = mixed_cnt[slot];
-          const int cell = mixed_cell[slot];
-          float a = __ldcg(&grid[cell]);
+        } else {
+          const int slot = v[u] & 0x7fffffff;
+          const int n = cnt[slot];
+          int32_t* ev = events + off[slot];
           if (n <= 16) {
             int e[16];
 #pragma unroll
@@ -325,30 +410,21 @@ __global__ void __launch_bounds__(kThreads, 1) ogm_build_kernel(const OgmParams 
               a = apply_updates(a, 1, (pick & 1) ? kLogOdds : -kLogOdds);
             }
           } else {
-            int32_t* evw = events + mixed_off[slot];
             for (int i = 1; i < n; ++i) {                           // insertion sort by ray index
-              const int key = evw[i];
+              const int key = ev[i];
               int j = i - 1;
-              while (j >= 0 && evw[j] > key) { evw[j + 1] = evw[j]; --j; }
-              evw[j + 1] = key;
+              while (j >= 0 && ev[j] > key) { ev[j + 1] = ev[j]; --j; }
+              ev[j + 1] = key;
             }
-            for (int i = 0; i < n; ++i) a = apply_updates(a, 1, (evw[i] & 1) ? kLogOdds : -kLogOdds);
+            for (int i = 0; i < n; ++i) a = apply_updates(a, 1, (ev[i] & 1) ? kLogOdds : -kLogOdds);
           }
-          grid[cell] = clip20(a);
-          scratch[cell] = 0;
         }
-        __threadfence();
+        a = clip20(a);                                              // modules/ogm.py:191, after every scan
+        planes[(size_t)sl * cells + cell] = 0;                      // clean for the next batch
       }
-      cluster.sync();                                               // scan fully applied, scratch clean again
-      PH(4);
-      const int again = __ldcg(&ctl[2]);
-      if (!again) break;
-      cluster.sync();                                               // ctl[] is reset at the loop top
     }
+    if (loaded) grid[cell] = a;
   }
-#ifdef B200ICP_OGM_PROFILE
-  if (gtid == 0) for (int i = 0; i < 6; ++i) ctl[4 + i] = (int)(ph[i] / 1000);   // microseconds per phase
-#endif
 }
 
 __global__ void ogm_binarize_kernel(const float* __restrict__ log_odds, uint8_t* __restrict__ grid,
@@ -357,15 +433,50 @@ __global__ void ogm_binarize_kernel(const float* __restrict__ log_odds, uint8_t*
   if (i < n) grid[i] = log_odds[i] <= one_at_or_below ? 1 : 0;
 }
 
+struct OgmLayout {
+  int batch, slot_cap, ev_cap;
+  size_t off_planes, off_bbox, off_ctl, off_cnt, off_off, off_fill, off_events, total;   // in int32 elements
+};
+
+int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  if (!e || !*e) return dflt;
+  const int v = atoi(e);
+  return v < 0 ? dflt : v;
+}
+
+OgmLayout ogm_layout(int width, int height, int n_max, int n_maps) {
+  OgmLayout L;
+  const size_t cells = (size_t)width * height;
+  size_t b = kPlaneBudget / (cells * sizeof(int32_t));
+  L.batch = (int)(b < 1 ? 1 : (b > (size_t)kBatchMax ? (size_t)kBatchMax : b));
+  // capacities of the event lists (tuning / test knobs: the overflow path is exact whatever they are)
+  L.slot_cap = L.batch * env_int("B200ICP_OGM_SLOTS_PER_SCAN", kSlotsPerScan);
+  L.ev_cap = L.batch * n_max * env_int("B200ICP_OGM_EVENTS_PER_RAY", kEventsPerRay);
+  if (L.slot_cap < 1) L.slot_cap = 1;
+  if (L.ev_cap < 1) L.ev_cap = 1;
+  size_t o = 0;
+  auto take = [&](size_t n) { const size_t at = o; o += (n + 31) / 32 * 32; return at; };
+  L.off_planes = take((size_t)n_maps * L.batch * cells);
+  L.off_bbox = take((size_t)n_maps * L.batch * 4);
+  L.off_ctl = take((size_t)n_maps * 4);
+  L.off_cnt = take((size_t)n_maps * L.slot_cap);
+  L.off_off = take((size_t)n_maps * L.slot_cap);
+  L.off_fill = take((size_t)n_maps * L.slot_cap);
+  L.off_events = take((size_t)n_maps * L.ev_cap);
+  L.total = o;
+  return L;
+}
+
 }  // namespace
 
 extern "C" {
 
 int b200icp_ogm_workspace_bytes(int width, int height, int n_max, int n_maps, size_t* bytes_out) {
-  if (!bytes_out || width <= 0 || height <= 0 || n_max <= 0 || n_maps <= 0) return B200ICP_ERR_BAD_ARG;
-  const size_t ev_cap = (size_t)n_max * 64 + 65536;
-  const size_t per_map = (size_t)width * height + 16 + 4 * (size_t)kMixedCap + ev_cap;
-  *bytes_out = per_map * sizeof(int32_t) * (size_t)n_maps;
+  if (!bytes_out || width <= 0 || height <= 0 || n_max <= 0 || n_maps <= 0 || n_max > 32767)
+    return B200ICP_ERR_BAD_ARG;
+  if ((long long)width * height > 0x7fffffffLL) return B200ICP_ERR_TOO_LARGE;
+  *bytes_out = ogm_layout(width, height, n_max, n_maps).total * sizeof(int32_t);
   return B200ICP_OK;
 }
 
@@ -374,37 +485,37 @@ int b200icp_ogm_build(float* log_odds, int width, int height, double res, double
                       const int32_t* counts, int n_scans, int n_max, int n_maps, void* workspace,
                       size_t workspace_bytes, void* stream) {
   if (!log_odds || !poses || !cos_sin || !scans || !counts || width <= 0 || height <= 0 ||
-      !(res > 0.0) || n_scans < 0 || n_max <= 0 || n_maps <= 0 || n_max > 32767)
+      !(res > 0.0) || n_scans < 0 || n_max <= 0 || n_maps <= 0 || n_max > 32767 || n_maps > 65535)
     return B200ICP_ERR_BAD_ARG;
   if ((long long)width * height > 0x7fffffffLL) return B200ICP_ERR_TOO_LARGE;
-  size_t need = 0;
-  b200icp_ogm_workspace_bytes(width, height, n_max, n_maps, &need);
-  if (!workspace || workspace_bytes < need) return B200ICP_ERR_WORKSPACE;
+  const OgmLayout L = ogm_layout(width, height, n_max, n_maps);
+  if (!workspace || workspace_bytes < L.total * sizeof(int32_t)) return B200ICP_ERR_WORKSPACE;
   if (n_scans == 0) return B200ICP_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (cudaMemsetAsync(workspace, 0, need, st) != cudaSuccess) return B200ICP_ERR_CUDA;
+  int32_t* ws = static_cast<int32_t*>(workspace);
+  const size_t cells = (size_t)width * height;
+  if (cudaMemsetAsync(ws + L.off_planes, 0, (size_t)n_maps * L.batch * cells * sizeof(int32_t), st) != cudaSuccess)
+    return B200ICP_ERR_CUDA;
   OgmParams p{};
   p.log_odds = log_odds; p.width = width; p.height = height; p.res = res; p.min_x = min_x; p.min_y = min_y;
   p.poses = poses; p.cs = cos_sin; p.scans = scans; p.counts = counts;
-  p.n_scans = n_scans; p.n_max = n_max; p.n_maps = n_maps;
-  p.workspace = static_cast<int32_t*>(workspace);
-  p.ev_cap = n_max * 64 + 65536;
-  p.ws_stride = (long long)width * height + 16 + 4LL * kMixedCap + p.ev_cap;
-  const size_t smem = (size_t)n_max * sizeof(int2);
-  if (cudaFuncSetAttribute(ogm_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
-    return B200ICP_ERR_TOO_LARGE;
-  if (cudaFuncSetAttribute(ogm_build_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
-    return B200ICP_ERR_CUDA;
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)n_maps * kCluster);
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr{};
-  attr.id = cudaLaunchAttributeClusterDimension;
-  attr.val.clusterDim.x = kCluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
-  cfg.attrs = &attr; cfg.numAttrs = 1;
-  if (cudaLaunchKernelEx(&cfg, ogm_build_kernel, p) != cudaSuccess) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
+  p.n_scans = n_scans; p.n_max = n_max; p.n_maps = n_maps; p.batch = L.batch;
+  p.planes = ws + L.off_planes; p.bbox = ws + L.off_bbox; p.ctl = ws + L.off_ctl;
+  p.slot_cnt = ws + L.off_cnt; p.slot_off = ws + L.off_off; p.slot_fill = ws + L.off_fill;
+  p.events = ws + L.off_events; p.slot_cap = L.slot_cap; p.ev_cap = L.ev_cap;
+  const unsigned ray_blocks = (unsigned)((n_max + kThreads - 1) / kThreads);
+  const size_t cell_blocks = (cells + kThreads - 1) / kThreads;
+  const unsigned sweep_blocks = (unsigned)(cell_blocks < 64 ? cell_blocks : 64);
+  const unsigned apply_blocks = (unsigned)(cell_blocks < 148 * 8 ? cell_blocks : 148 * 8);
+  for (int s0 = 0; s0 < n_scans; s0 += L.batch) {
+    p.s0 = s0;
+    p.sb = n_scans - s0 < L.batch ? n_scans - s0 : L.batch;
+    ogm_reset_kernel<<<1, kThreads, 0, st>>>(p);
+    ogm_count_kernel<<<dim3(ray_blocks, (unsigned)p.sb, (unsigned)n_maps), kThreads, 0, st>>>(p);
+    ogm_classify_kernel<<<dim3(sweep_blocks, (unsigned)p.sb, (unsigned)n_maps), kThreads, 0, st>>>(p);
+    ogm_event_kernel<<<dim3(ray_blocks, (unsigned)p.sb, (unsigned)n_maps), kThreads, 0, st>>>(p);
+    ogm_apply_kernel<<<dim3(apply_blocks, 1, (unsigned)n_maps), kThreads, 0, st>>>(p);
+  }
   return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
 }
 

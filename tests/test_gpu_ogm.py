@@ -48,7 +48,7 @@ def test_update_map_incremental_equals_build_map(ogm_golden):
 
 
 def test_batched_maps_and_oracle_on_fresh_inputs():
-    """Three pose sequences over the same scans in one launch (one CTA per map); each equals the
+    """Three pose sequences over the same scans in one launch (the maps share every launch); each equals the
     oracle run alone.  Includes an empty scan and rays that start outside the grid."""
     from lidar_slam_b200 import ogm, synth
     n = 10
@@ -93,3 +93,37 @@ def test_full_size_properties():
     o.build_map(poses[:2], z)
     mm.build_map(poses[:2], z)
     assert np.array_equal(mm.grid_map_log_odds, o.log_odds) and np.array_equal(mm.grid_map, o.grid)
+
+
+def test_event_list_overflow_path_is_exact(ogm_golden, monkeypatch):
+    """With no room for event lists every cell that sees both signs in one scan is replayed by the
+    closed-form ray test; with room for only a few lists both paths mix.  Same bits either way."""
+    from lidar_slam_b200.ogm import OccupancyGridMap
+    g = ogm_golden
+    for per_ray, slots in (("0", "4096"), ("16", "1")):
+        monkeypatch.setenv("B200ICP_OGM_EVENTS_PER_RAY", per_ray)
+        monkeypatch.setenv("B200ICP_OGM_SLOTS_PER_SCAN", slots)
+        for name in map(str, g["names"]):
+            res, mxx, mxy, mnx, mny = g[f"{name}/params"]
+            m = OccupancyGridMap(res, mxx, mxy, mnx, mny)
+            m.build_map(g[f"{name}/poses"], split(g[f"{name}/points"], g[f"{name}/counts"]))
+            assert np.array_equal(m.grid_map_log_odds, g[f"{name}/log_odds"]), (per_ray, slots, name)
+
+
+def test_many_scans_cross_batch_boundaries():
+    """More scans than one batch holds (64): the planes are reused batch after batch; equals the
+    oracle on every cell."""
+    from lidar_slam_b200 import ogm, synth
+    n = 150
+    poses = synth.make_trajectories(1, n, seed=4)[0]
+    poses[:, :2] *= 0.5
+    scans, counts = synth.cast_scans(poses, seed=4)
+    scans, counts = scans.numpy(), counts.numpy()
+    meas = [scans[i, :counts[i]][::9] for i in range(n)]
+    res, box = 0.1, (6.0, 4.0, -6.0, -4.0)
+    o = oo.OgmOracle(res, *box)
+    o.build_map(poses, meas)
+    m = ogm.OccupancyGridMap(res, *box)
+    m.build_map(poses, meas)
+    assert np.array_equal(m.grid_map_log_odds, o.log_odds)
+    assert np.array_equal(m.grid_map, o.grid)
