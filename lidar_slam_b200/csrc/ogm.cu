@@ -321,6 +321,33 @@ __global__ void __launch_bounds__(kThreads) ogm_event_kernel(const OgmParams p) 
               p.slot_fill + (size_t)map * p.slot_cap, p.events + (size_t)map * p.ev_cap);
 }
 
+// Replay the n <= N events of one (scan, cell) in ray order: a bitonic network in registers
+// sorts the (ray << 1 | sign) words (ray indices are distinct; the padding sorts last).
+template <int N>
+__device__ __forceinline__ float replay_sorted(float a, const int32_t* ev, int n) {
+  int e[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) e[i] = i < n ? __ldcg(&ev[i]) : 0x7fffffff;
+#pragma unroll
+  for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const int l = i ^ j;
+        if (l > i) {
+          const int lo = min(e[i], e[l]), hi = max(e[i], e[l]);
+          if ((i & k) == 0) { e[i] = lo; e[l] = hi; } else { e[i] = hi; e[l] = lo; }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+    if (i < n) a = apply_updates(a, 1, (e[i] & 1) ? kLogOdds : -kLogOdds);
+  return a;
+}
+
 // apply: grid (cell blocks, 1, maps); one thread per cell of the union of the batch's windows
 __global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) {
   __shared__ Window win[kBatchMax];
@@ -393,22 +420,12 @@ __global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) 
           const int slot = v[u] & 0x7fffffff;
           const int n = cnt[slot];
           int32_t* ev = events + off[slot];
-          if (n <= 16) {
-            int e[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) e[i] = i < n ? __ldcg(&ev[i]) : 0x7fffffff;
-            // rank sort: ray indices are distinct, so the rank of an event is its position
-            for (int want = 0; want < n; ++want) {
-              int pick = 0;
-#pragma unroll
-              for (int i = 0; i < 16; ++i) {
-                int rank = 0;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) rank += (e[j] < e[i]) ? 1 : 0;
-                if (rank == want) pick = e[i];
-              }
-              a = apply_updates(a, 1, (pick & 1) ? kLogOdds : -kLogOdds);
-            }
+          if (n <= 4) {
+            a = replay_sorted<4>(a, ev, n);
+          } else if (n <= 8) {
+            a = replay_sorted<8>(a, ev, n);
+          } else if (n <= 16) {
+            a = replay_sorted<16>(a, ev, n);
           } else {
             for (int i = 1; i < n; ++i) {                           // insertion sort by ray index
               const int key = ev[i];
