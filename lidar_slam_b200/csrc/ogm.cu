@@ -37,11 +37,9 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kBatchMax = 64;                     // scans per batch (count planes per map)
 constexpr size_t kPlaneBudget = (size_t)96 << 20; // bytes of count planes per map that set the batch size
-constexpr int kSlotsPerScan = 4096;               // event lists per scan of the batch (average)
-constexpr int kEventsPerRay = 16;                 // event capacity per ray of the batch (average)
+constexpr int kEventsPerRay = 16;                 // event words per ray of the batch (average capacity)
 constexpr unsigned kOverflowTag = 0xffffffffu;
 constexpr double kLogOdds = 1.3862943611198906;   // np.log(4.)  (modules/ogm.py:44)
-constexpr int kSaturate = 30;                     // 30 * log 4 = 41.6 > 40 = the width of the clip interval
 
 struct OgmParams {
   float* log_odds;        // [n_maps][width*height]
@@ -56,12 +54,9 @@ struct OgmParams {
   int batch;              // planes per map (capacity)
   int32_t* planes;        // [n_maps][batch][width*height]  dec count | inc count << 16, or tag
   int32_t* bbox;          // [n_maps][batch][4]  min x, min -x, min y, min -y of the visited window
-  int32_t* ctl;           // [n_maps][4]  event lists used, events used
-  int32_t* slot_cnt;      // [n_maps][slot_cap]
-  int32_t* slot_off;      // [n_maps][slot_cap]
-  int32_t* slot_fill;     // [n_maps][slot_cap]
-  int32_t* events;        // [n_maps][ev_cap]
-  int slot_cap, ev_cap;
+  int32_t* ctl;           // [n_maps][4]  event lists made, event words used
+  int32_t* events;        // [n_maps][ev_cap + 32]  lists: [fill counter == n after the event pass][n events]
+  int ev_cap;
 };
 
 // modules/ogm.py:104-126: ceil((x - min)/res) - 1 (float64 arithmetic, then integer)
@@ -170,8 +165,7 @@ __device__ __forceinline__ int2 ray_end(const OgmParams& p, const ScanFrame& f, 
 // dx, m its quotient).  MODE 0 counts visits on the plane, MODE 1 appends (ray, sign) events to
 // the tagged cells.
 template <int MODE>
-__device__ __forceinline__ void walk_ray(const Ray& r, int ray, int height, int32_t* plane,
-                                         const int32_t* slot_off, int32_t* slot_fill, int32_t* events) {
+__device__ __forceinline__ void walk_ray(const Ray& r, int ray, int height, int32_t* plane, int32_t* events) {
   if (r.klo > r.khi) return;
   const int dx = r.dx, dy = r.dy;
   int m = 0, rem = r.c0;
@@ -206,9 +200,9 @@ __device__ __forceinline__ void walk_ray(const Ray& r, int ray, int height, int3
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         if (tags[u] < 0 && (unsigned)tags[u] != kOverflowTag) {
-          const int slot = tags[u] & 0x7fffffff;
-          const int pos = atomicAdd(&slot_fill[slot], 1);
-          events[slot_off[slot] + pos] = (ray << 1) | ((k0 + u == r.khi) ? 1 : 0);
+          int32_t* list = events + (tags[u] & 0x7fffffff);
+          const int pos = atomicAdd(&list[0], 1);
+          list[1 + pos] = (ray << 1) | ((k0 + u == r.khi) ? 1 : 0);
         }
       }
     }
@@ -256,7 +250,7 @@ __global__ void __launch_bounds__(kThreads) ogm_count_kernel(const OgmParams p) 
     const int2 e = ray_end(p, f, s, ray);
     b0 = min(b0, e.x); b1 = min(b1, -e.x); b2 = min(b2, e.y); b3 = min(b3, -e.y);
     const Ray r = make_ray(f.sx, f.sy, e.x, e.y, p.width, p.height);
-    walk_ray<0>(r, ray, p.height, plane, nullptr, nullptr, nullptr);
+    walk_ray<0>(r, ray, p.height, plane, nullptr);
   }
   b0 = warp_min_i(b0); b1 = warp_min_i(b1); b2 = warp_min_i(b2); b3 = warp_min_i(b3);
   if ((threadIdx.x & 31) == 0) {
@@ -284,9 +278,7 @@ __global__ void __launch_bounds__(kThreads) ogm_classify_kernel(const OgmParams 
   const size_t cells = (size_t)p.width * p.height;
   int32_t* plane = p.planes + ((size_t)map * p.batch + sl) * cells;
   int32_t* ctl = p.ctl + map * 4;
-  int32_t* cnt = p.slot_cnt + (size_t)map * p.slot_cap;
-  int32_t* off = p.slot_off + (size_t)map * p.slot_cap;
-  int32_t* fill = p.slot_fill + (size_t)map * p.slot_cap;
+  int32_t* events = p.events + (size_t)map * (p.ev_cap + 32);
   for (int t = blockIdx.x * kThreads + threadIdx.x; t < wcells; t += gridDim.x * kThreads) {
     const int cell = (w.x0 + t / wh) * p.height + w.y0 + t % wh;
     const int v = __ldcg(&plane[cell]);
@@ -294,13 +286,12 @@ __global__ void __launch_bounds__(kThreads) ogm_classify_kernel(const OgmParams 
     if (dec == 0 || inc == 0) continue;
     const int n = dec + inc;
     unsigned tag = kOverflowTag;
-    const int o = atomicAdd(&ctl[1], n);
-    if (o + n <= p.ev_cap) {
-      const int slot = atomicAdd(&ctl[0], 1);
-      if (slot < p.slot_cap) {
-        cnt[slot] = n; off[slot] = o; fill[slot] = 0;
-        tag = 0x80000000u | (unsigned)slot;
-      }
+    // the list: one word that counts the appended events (== n once the event pass is done), then n events
+    const unsigned o = (unsigned)atomicAdd(&ctl[1], n + 1);
+    if (o <= (unsigned)p.ev_cap && o + (unsigned)n + 1u <= (unsigned)p.ev_cap) {
+      events[o] = 0;
+      tag = 0x80000000u | o;
+      ctl[0] = 1;
     }
     plane[cell] = (int)tag;
   }
@@ -317,17 +308,19 @@ __global__ void __launch_bounds__(kThreads) ogm_event_kernel(const OgmParams p) 
   int32_t* plane = p.planes + ((size_t)map * p.batch + sl) * cells;
   const int2 e = ray_end(p, f, s, ray);
   const Ray r = make_ray(f.sx, f.sy, e.x, e.y, p.width, p.height);
-  walk_ray<1>(r, ray, p.height, plane, p.slot_off + (size_t)map * p.slot_cap,
-              p.slot_fill + (size_t)map * p.slot_cap, p.events + (size_t)map * p.ev_cap);
+  walk_ray<1>(r, ray, p.height, plane, p.events + (size_t)map * (p.ev_cap + 32));
 }
 
 // Replay the n <= N events of one (scan, cell) in ray order: a bitonic network in registers
 // sorts the (ray << 1 | sign) words (ray indices are distinct; the padding sorts last).
 template <int N>
-__device__ __forceinline__ float replay_sorted(float a, const int32_t* ev, int n) {
+__device__ __forceinline__ float replay_sorted(float a, const int32_t* ev, int n, const int (&first)[4]) {
   int e[N];
 #pragma unroll
-  for (int i = 0; i < N; ++i) e[i] = i < n ? __ldcg(&ev[i]) : 0x7fffffff;
+  for (int i = 0; i < N; ++i) {
+    const int w = i < 4 ? first[i] : __ldcg(&ev[i]);    // the list area is padded: reads past n are harmless
+    e[i] = i < n ? w : 0x7fffffff;
+  }
 #pragma unroll
   for (int k = 2; k <= N; k <<= 1) {
 #pragma unroll
@@ -371,9 +364,7 @@ __global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) 
   const size_t cells = (size_t)p.width * p.height;
   float* grid = p.log_odds + (size_t)map * cells;
   int32_t* planes = p.planes + (size_t)map * p.batch * cells;
-  const int32_t* cnt = p.slot_cnt + (size_t)map * p.slot_cap;
-  const int32_t* off = p.slot_off + (size_t)map * p.slot_cap;
-  int32_t* events = p.events + (size_t)map * p.ev_cap;
+  int32_t* events = p.events + (size_t)map * (p.ev_cap + 32);
 
   for (int t = blockIdx.x * kThreads + tid; t < ucells; t += gridDim.x * kThreads) {
     const int cx = ux0 + t / uh, cy = uy0 + t % uh;
@@ -400,12 +391,14 @@ __global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) 
         if (v[u] == 0) continue;
         const int sl = s8 + u;
         if (v[u] > 0) {
-          // only decrements or only increments.  The cell enters a scan inside [-20, 20] and every
-          // update moves by log 4 (up to an ulp): after 30 same-sign updates the value is beyond
-          // the clip whatever it started from
+          // only decrements or only increments: the order among identical updates is immaterial.
+          // The clip comes after the scan, so when  a -/+ k log 4  lands beyond it by more than the
+          // k roundings can move it (< k * 2^-18), the result is the clip value whatever the
+          // roundings were -- the usual case for the cells around the robot, which sit at -20.
           const int dec = v[u] & 0xffff, inc = (v[u] >> 16) & 0x7fff;
-          if (dec >= kSaturate) a = -20.0f;
-          else if (inc >= kSaturate) a = 20.0f;
+          const double est = dec ? (double)a - (double)dec * kLogOdds : (double)a + (double)inc * kLogOdds;
+          if (est < -20.5) a = -20.0f;
+          else if (est > 20.5) a = 20.0f;
           else a = dec ? apply_updates(a, dec, -kLogOdds) : apply_updates(a, inc, kLogOdds);
         } else if ((unsigned)v[u] == kOverflowTag) {
           // no room for an event list: test every ray of the scan against this cell, in ray order
@@ -417,15 +410,17 @@ __global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) 
             if (hit) a = apply_updates(a, 1, hit > 0 ? kLogOdds : -kLogOdds);
           }
         } else {
-          const int slot = v[u] & 0x7fffffff;
-          const int n = cnt[slot];
-          int32_t* ev = events + off[slot];
+          int32_t* list = events + (v[u] & 0x7fffffff);
+          // counter word and the first four events in one round trip (most lists are that short)
+          const int n = __ldcg(&list[0]);
+          const int first[4] = {__ldcg(&list[1]), __ldcg(&list[2]), __ldcg(&list[3]), __ldcg(&list[4])};
+          int32_t* ev = list + 1;
           if (n <= 4) {
-            a = replay_sorted<4>(a, ev, n);
+            a = replay_sorted<4>(a, ev, n, first);
           } else if (n <= 8) {
-            a = replay_sorted<8>(a, ev, n);
+            a = replay_sorted<8>(a, ev, n, first);
           } else if (n <= 16) {
-            a = replay_sorted<16>(a, ev, n);
+            a = replay_sorted<16>(a, ev, n, first);
           } else {
             for (int i = 1; i < n; ++i) {                           // insertion sort by ray index
               const int key = ev[i];
@@ -451,8 +446,8 @@ __global__ void ogm_binarize_kernel(const float* __restrict__ log_odds, uint8_t*
 }
 
 struct OgmLayout {
-  int batch, slot_cap, ev_cap;
-  size_t off_planes, off_bbox, off_ctl, off_cnt, off_off, off_fill, off_events, total;   // in int32 elements
+  int batch, ev_cap;
+  size_t off_planes, off_bbox, off_ctl, off_events, total;   // in int32 elements
 };
 
 int env_int(const char* name, int dflt) {
@@ -467,20 +462,15 @@ OgmLayout ogm_layout(int width, int height, int n_max, int n_maps) {
   const size_t cells = (size_t)width * height;
   size_t b = kPlaneBudget / (cells * sizeof(int32_t));
   L.batch = (int)(b < 1 ? 1 : (b > (size_t)kBatchMax ? (size_t)kBatchMax : b));
-  // capacities of the event lists (tuning / test knobs: the overflow path is exact whatever they are)
-  L.slot_cap = L.batch * env_int("B200ICP_OGM_SLOTS_PER_SCAN", kSlotsPerScan);
-  L.ev_cap = L.batch * n_max * env_int("B200ICP_OGM_EVENTS_PER_RAY", kEventsPerRay);
-  if (L.slot_cap < 1) L.slot_cap = 1;
-  if (L.ev_cap < 1) L.ev_cap = 1;
+  // capacity of the event lists (tuning / test knob: the overflow path is exact whatever it is)
+  const long long cap = (long long)L.batch * n_max * env_int("B200ICP_OGM_EVENTS_PER_RAY", kEventsPerRay);
+  L.ev_cap = (int)(cap < 1 ? 1 : (cap > 0x3fffffffLL ? 0x3fffffffLL : cap));
   size_t o = 0;
   auto take = [&](size_t n) { const size_t at = o; o += (n + 31) / 32 * 32; return at; };
   L.off_planes = take((size_t)n_maps * L.batch * cells);
   L.off_bbox = take((size_t)n_maps * L.batch * 4);
   L.off_ctl = take((size_t)n_maps * 4);
-  L.off_cnt = take((size_t)n_maps * L.slot_cap);
-  L.off_off = take((size_t)n_maps * L.slot_cap);
-  L.off_fill = take((size_t)n_maps * L.slot_cap);
-  L.off_events = take((size_t)n_maps * L.ev_cap);
+  L.off_events = take((size_t)n_maps * ((size_t)L.ev_cap + 32));
   L.total = o;
   return L;
 }
@@ -518,8 +508,7 @@ int b200icp_ogm_build(float* log_odds, int width, int height, double res, double
   p.poses = poses; p.cs = cos_sin; p.scans = scans; p.counts = counts;
   p.n_scans = n_scans; p.n_max = n_max; p.n_maps = n_maps; p.batch = L.batch;
   p.planes = ws + L.off_planes; p.bbox = ws + L.off_bbox; p.ctl = ws + L.off_ctl;
-  p.slot_cnt = ws + L.off_cnt; p.slot_off = ws + L.off_off; p.slot_fill = ws + L.off_fill;
-  p.events = ws + L.off_events; p.slot_cap = L.slot_cap; p.ev_cap = L.ev_cap;
+  p.events = ws + L.off_events; p.ev_cap = L.ev_cap;
   const unsigned ray_blocks = (unsigned)((n_max + kThreads - 1) / kThreads);
   const size_t cell_blocks = (cells + kThreads - 1) / kThreads;
   const unsigned sweep_blocks = (unsigned)(cell_blocks < 64 ? cell_blocks : 64);

@@ -100,14 +100,13 @@ def test_event_list_overflow_path_is_exact(ogm_golden, monkeypatch):
     closed-form ray test; with room for only a few lists both paths mix.  Same bits either way."""
     from lidar_slam_b200.ogm import OccupancyGridMap
     g = ogm_golden
-    for per_ray, slots in (("0", "4096"), ("16", "1")):
+    for per_ray in ("0", "1"):
         monkeypatch.setenv("B200ICP_OGM_EVENTS_PER_RAY", per_ray)
-        monkeypatch.setenv("B200ICP_OGM_SLOTS_PER_SCAN", slots)
         for name in map(str, g["names"]):
             res, mxx, mxy, mnx, mny = g[f"{name}/params"]
             m = OccupancyGridMap(res, mxx, mxy, mnx, mny)
             m.build_map(g[f"{name}/poses"], split(g[f"{name}/points"], g[f"{name}/counts"]))
-            assert np.array_equal(m.grid_map_log_odds, g[f"{name}/log_odds"]), (per_ray, slots, name)
+            assert np.array_equal(m.grid_map_log_odds, g[f"{name}/log_odds"]), (per_ray, name)
 
 
 def test_many_scans_cross_batch_boundaries():
