@@ -55,7 +55,7 @@ struct OgmParams {
   int32_t* planes;        // [n_maps][batch][width*height]  dec count | inc count << 16, or tag
   int32_t* bbox;          // [n_maps][batch][4]  min x, min -x, min y, min -y of the visited window
   int32_t* ctl;           // [n_maps][4]  event lists made, event words used
-  int32_t* events;        // [n_maps][ev_cap + 32]  lists: [fill counter == n after the event pass][n events]
+  int32_t* events;        // [n_maps][ev_cap + 32]  lists: [fill counter == n after the event pass][increments][n events]
   int ev_cap;
 };
 
@@ -202,7 +202,7 @@ __device__ __forceinline__ void walk_ray(const Ray& r, int ray, int height, int3
         if (tags[u] < 0 && (unsigned)tags[u] != kOverflowTag) {
           int32_t* list = events + (tags[u] & 0x7fffffff);
           const int pos = atomicAdd(&list[0], 1);
-          list[1 + pos] = (ray << 1) | ((k0 + u == r.khi) ? 1 : 0);
+          list[2 + pos] = (ray << 1) | ((k0 + u == r.khi) ? 1 : 0);
         }
       }
     }
@@ -279,21 +279,49 @@ __global__ void __launch_bounds__(kThreads) ogm_classify_kernel(const OgmParams 
   int32_t* plane = p.planes + ((size_t)map * p.batch + sl) * cells;
   int32_t* ctl = p.ctl + map * 4;
   int32_t* events = p.events + (size_t)map * (p.ev_cap + 32);
-  for (int t = blockIdx.x * kThreads + threadIdx.x; t < wcells; t += gridDim.x * kThreads) {
-    const int cell = (w.x0 + t / wh) * p.height + w.y0 + t % wh;
-    const int v = __ldcg(&plane[cell]);
-    const int dec = v & 0xffff, inc = (v >> 16) & 0x7fff;
-    if (dec == 0 || inc == 0) continue;
-    const int n = dec + inc;
-    unsigned tag = kOverflowTag;
-    // the list: one word that counts the appended events (== n once the event pass is done), then n events
-    const unsigned o = (unsigned)atomicAdd(&ctl[1], n + 1);
-    if (o <= (unsigned)p.ev_cap && o + (unsigned)n + 1u <= (unsigned)p.ev_cap) {
-      events[o] = 0;
-      tag = 0x80000000u | o;
-      ctl[0] = 1;
+  // four independent loads in flight per thread; the list area is reserved with ONE atomic per
+  // warp (prefix sum over the lanes that need a list): the counter is a single hot address
+  const int lane = threadIdx.x & 31;
+  const int stride = gridDim.x * kThreads;
+  for (int t0 = blockIdx.x * kThreads + threadIdx.x; t0 - (int)threadIdx.x < wcells; t0 += 4 * stride) {
+    int cell[4], v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t0 + u * stride;
+      cell[u] = -1; v[u] = 0;
+      if (t < wcells) {
+        cell[u] = (w.x0 + t / wh) * p.height + w.y0 + t % wh;
+        v[u] = __ldcg(&plane[cell[u]]);
+      }
     }
-    plane[cell] = (int)tag;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int dec = v[u] & 0xffff, inc = (v[u] >> 16) & 0x7fff;
+      const bool mixed = dec != 0 && inc != 0;
+      const unsigned need = __ballot_sync(0xffffffffu, mixed);
+      if (need == 0) continue;
+      const int words = mixed ? dec + inc + 2 : 0;       // fill counter, increment count, events
+      int pre = words;                                    // inclusive prefix sum over the warp
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, pre, o);
+        if (lane >= o) pre += up;
+      }
+      const int total = __shfl_sync(0xffffffffu, pre, 31);
+      unsigned base = 0;
+      if (lane == 0) { base = (unsigned)atomicAdd(&ctl[1], total); ctl[0] = 1; }
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (mixed) {
+        const unsigned o = base + (unsigned)(pre - words);
+        unsigned tag = kOverflowTag;
+        if (o <= (unsigned)p.ev_cap && o + (unsigned)words <= (unsigned)p.ev_cap) {
+          events[o] = 0;
+          events[o + 1] = inc;
+          tag = 0x80000000u | o;
+        }
+        plane[cell[u]] = (int)tag;
+      }
+    }
   }
 }
 
@@ -338,6 +366,55 @@ __device__ __forceinline__ float replay_sorted(float a, const int32_t* ev, int n
 #pragma unroll
   for (int i = 0; i < N; ++i)
     if (i < n) a = apply_updates(a, 1, (e[i] & 1) ? kLogOdds : -kLogOdds);
+  return a;
+}
+
+// Long lists with few increments: only the interleaving of the signs matters, so the increments
+// (<= 16) are sorted and every decrement is counted into the gap between two of them.
+__device__ __forceinline__ float replay_by_gaps(float a, const int32_t* ev, int n) {
+  int incr[16], gap[17];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) incr[j] = 0x7fffffff;
+#pragma unroll
+  for (int j = 0; j < 17; ++j) gap[j] = 0;
+  int ni = 0;
+  for (int i = 0; i < n; ++i) {
+    const int w = __ldcg(&ev[i]);
+    if (w & 1) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) if (j == ni) incr[j] = w;
+      ++ni;
+    }
+  }
+#pragma unroll
+  for (int k = 2; k <= 16; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int l = i ^ j;
+        if (l > i) {
+          const int lo = min(incr[i], incr[l]), hi = max(incr[i], incr[l]);
+          if ((i & k) == 0) { incr[i] = lo; incr[l] = hi; } else { incr[i] = hi; incr[l] = lo; }
+        }
+      }
+    }
+  }
+  for (int i = 0; i < n; ++i) {
+    const int w = __ldcg(&ev[i]);
+    if (!(w & 1)) {
+      int rank = 0;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) rank += (incr[j] < w) ? 1 : 0;
+#pragma unroll
+      for (int j = 0; j < 17; ++j) gap[j] += (rank == j) ? 1 : 0;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 17; ++j) {
+    a = apply_updates(a, gap[j], -kLogOdds);
+    if (j < ni) a = apply_updates(a, 1, kLogOdds);
+  }
   return a;
 }
 
@@ -410,23 +487,35 @@ __global__ void __launch_bounds__(kThreads) ogm_apply_kernel(const OgmParams p) 
             if (hit) a = apply_updates(a, 1, hit > 0 ? kLogOdds : -kLogOdds);
           }
         } else {
+          // counter, increments and the first four events in one round trip (most lists are short)
           int32_t* list = events + (v[u] & 0x7fffffff);
-          // counter word and the first four events in one round trip (most lists are that short)
-          const int n = __ldcg(&list[0]);
-          const int first[4] = {__ldcg(&list[1]), __ldcg(&list[2]), __ldcg(&list[3]), __ldcg(&list[4])};
-          int32_t* ev = list + 1;
-          if (n <= 4) {
+          const int n = __ldcg(&list[0]), inc = __ldcg(&list[1]), dec = n - inc;
+          const int first[4] = {__ldcg(&list[2]), __ldcg(&list[3]), __ldcg(&list[4]), __ldcg(&list[5])};
+          int32_t* ev = list + 2;
+          // The clip comes after the scan: when  a + (inc - dec) log 4  lands beyond it by more than
+          // the n roundings can move it (each < |value| * 2^-24, |value| <= 20 + 1.39 n), the result
+          // is the clip value whatever the order was.
+          const double nn = (double)n;
+          const double margin = 0.5 + nn * (20.0 + 1.4 * nn) * 5.9604644775390625e-08;
+          const double est = (double)a + (double)(inc - dec) * kLogOdds;
+          if (est < -20.0 - margin) {
+            a = -20.0f;
+          } else if (est > 20.0 + margin) {
+            a = 20.0f;
+          } else if (n <= 4) {
             a = replay_sorted<4>(a, ev, n, first);
           } else if (n <= 8) {
             a = replay_sorted<8>(a, ev, n, first);
           } else if (n <= 16) {
             a = replay_sorted<16>(a, ev, n, first);
+          } else if (inc <= 16) {
+            a = replay_by_gaps(a, ev, n);
           } else {
             for (int i = 1; i < n; ++i) {                           // insertion sort by ray index
               const int key = ev[i];
-              int j = i - 1;
-              while (j >= 0 && ev[j] > key) { ev[j + 1] = ev[j]; --j; }
-              ev[j + 1] = key;
+              int k = i - 1;
+              while (k >= 0 && ev[k] > key) { ev[k + 1] = ev[k]; --k; }
+              ev[k + 1] = key;
             }
             for (int i = 0; i < n; ++i) a = apply_updates(a, 1, (ev[i] & 1) ? kLogOdds : -kLogOdds);
           }

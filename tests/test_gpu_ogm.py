@@ -126,3 +126,30 @@ def test_many_scans_cross_batch_boundaries():
     m.build_map(poses, meas)
     assert np.array_equal(m.grid_map_log_odds, o.log_odds)
     assert np.array_equal(m.grid_map, o.grid)
+
+
+@pytest.mark.parametrize("short_every", [2, 12])
+def test_cells_with_long_mixed_event_lists(short_every):
+    """A dense fan of rays where every `short_every`-th ray stops on a near arc that the others
+    cross: the near-arc cells collect hundreds of interleaved decrements and increments per scan
+    (long event lists: the gap replay for few increments, the general sort for many), some scans
+    from close by so that the lists also meet cells far from the clip."""
+    from lidar_slam_b200 import ogm
+    rng = np.random.default_rng(short_every)
+    n_scans, n_rays = 12, 900
+    ang = np.linspace(-0.35, 0.35, n_rays)
+    meas, poses = [], []
+    for s in range(n_scans):
+        near = 0.9 + 0.05 * rng.random(n_rays)
+        far = 2.4 + 0.3 * rng.random(n_rays)
+        r = np.where(np.arange(n_rays) % short_every == (s % short_every), near, far)
+        meas.append(np.stack([r * np.cos(ang), r * np.sin(ang)], axis=1))
+        poses.append([-1.0 + 0.02 * s, 0.03 * s, 0.1 * np.sin(s)])
+    poses = np.array(poses)
+    res, box = 0.1, (3.0, 2.0, -3.0, -2.0)
+    o = oo.OgmOracle(res, *box)
+    o.build_map(poses, meas)
+    m = ogm.OccupancyGridMap(res, *box)
+    m.build_map(poses, meas)
+    assert np.array_equal(m.grid_map_log_odds, o.log_odds)
+    assert np.array_equal(m.grid_map, o.grid)
