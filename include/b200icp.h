@@ -189,7 +189,13 @@ int b200icp_range_filter(double* scans, int32_t* counts, int n_scans, int n_max,
  * poses    [n_maps, n_scans, 3] float64 (x, y, yaw);  cos_sin [n_maps, n_scans, 2] float64 =
  *          (cos yaw, sin yaw) evaluated by the caller (bit-identical to numpy's).
  * scans / counts: the scan pool of b200icp_run with dim == 2 (robot-frame end points).
- * n_max <= 32767.  Workspace from b200icp_ogm_workspace_bytes. */
+ * n_max <= 32767, n_maps <= 65535.  Workspace from b200icp_ogm_workspace_bytes (two sets of up to
+ * 64 int32 count planes per map, <= 48 MB per set and map, plus the event lists).  The scans are
+ * processed 64 at a time by four kernels; the per-cell replay of batch b runs on an internal
+ * auxiliary stream while the ray passes of batch b + 1 run on `stream`, and `stream` is joined
+ * with the auxiliary stream before the call returns (stream-ordered for the caller as usual).
+ * B200ICP_OGM_EVENTS_PER_RAY (default 16) sizes the event lists; lists that do not fit are
+ * replayed by an exact closed-form ray test instead. */
 int b200icp_ogm_workspace_bytes(int width, int height, int n_max, int n_maps, size_t* bytes_out);
 int b200icp_ogm_build(float* log_odds, int width, int height, double res, double min_x, double min_y,
                       const double* poses, const double* cos_sin, const double* scans,

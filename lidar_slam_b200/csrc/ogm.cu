@@ -30,13 +30,15 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "../../include/b200icp.h"
 
 namespace {
 
 constexpr int kThreads = 256;
 constexpr int kBatchMax = 64;                     // scans per batch (count planes per map)
-constexpr size_t kPlaneBudget = (size_t)96 << 20; // bytes of count planes per map that set the batch size
+constexpr size_t kPlaneBudget = (size_t)48 << 20; // bytes of count planes per map and buffer set that set the batch size
 constexpr int kEventsPerRay = 16;                 // event words per ray of the batch (average capacity)
 constexpr unsigned kOverflowTag = 0xffffffffu;
 constexpr double kLogOdds = 1.3862943611198906;   // np.log(4.)  (modules/ogm.py:44)
@@ -536,8 +538,29 @@ __global__ void ogm_binarize_kernel(const float* __restrict__ log_odds, uint8_t*
 
 struct OgmLayout {
   int batch, ev_cap;
-  size_t off_planes, off_bbox, off_ctl, off_events, total;   // in int32 elements
+  size_t off_planes, off_bbox, off_ctl, off_events, set_stride, total;   // in int32 elements
 };
+
+// Two buffer sets: while the apply pass walks batch b on the auxiliary stream, the ray passes of
+// batch b + 1 fill the other set on the caller's stream (every pass alone leaves most SMs idle).
+struct OgmStreams {
+  cudaStream_t aux = nullptr;
+  cudaEvent_t ready[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr};
+};
+OgmStreams* ogm_streams() {
+  static OgmStreams per_device[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  OgmStreams& s = per_device[dev];
+  if (!s.aux) {
+    if (cudaStreamCreateWithFlags(&s.aux, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    for (int k = 0; k < 2; ++k) {
+      if (cudaEventCreateWithFlags(&s.ready[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+      if (cudaEventCreateWithFlags(&s.done[k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    }
+  }
+  return &s;
+}
 
 int env_int(const char* name, int dflt) {
   const char* e = getenv(name);
@@ -560,7 +583,8 @@ OgmLayout ogm_layout(int width, int height, int n_max, int n_maps) {
   L.off_bbox = take((size_t)n_maps * L.batch * 4);
   L.off_ctl = take((size_t)n_maps * 4);
   L.off_events = take((size_t)n_maps * ((size_t)L.ev_cap + 32));
-  L.total = o;
+  L.set_stride = o;
+  L.total = 2 * o;
   return L;
 }
 
@@ -590,27 +614,40 @@ int b200icp_ogm_build(float* log_odds, int width, int height, double res, double
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int32_t* ws = static_cast<int32_t*>(workspace);
   const size_t cells = (size_t)width * height;
-  if (cudaMemsetAsync(ws + L.off_planes, 0, (size_t)n_maps * L.batch * cells * sizeof(int32_t), st) != cudaSuccess)
-    return B200ICP_ERR_CUDA;
+  static std::mutex enqueue_mutex;      // the auxiliary stream and its events are shared per device
+  std::lock_guard<std::mutex> lock(enqueue_mutex);
+  OgmStreams* streams = ogm_streams();
+  if (!streams) return B200ICP_ERR_CUDA;
+  for (int k = 0; k < 2; ++k)
+    if (cudaMemsetAsync(ws + k * L.set_stride + L.off_planes, 0, (size_t)n_maps * L.batch * cells * sizeof(int32_t), st) != cudaSuccess)
+      return B200ICP_ERR_CUDA;
   OgmParams p{};
   p.log_odds = log_odds; p.width = width; p.height = height; p.res = res; p.min_x = min_x; p.min_y = min_y;
   p.poses = poses; p.cs = cos_sin; p.scans = scans; p.counts = counts;
-  p.n_scans = n_scans; p.n_max = n_max; p.n_maps = n_maps; p.batch = L.batch;
-  p.planes = ws + L.off_planes; p.bbox = ws + L.off_bbox; p.ctl = ws + L.off_ctl;
-  p.events = ws + L.off_events; p.ev_cap = L.ev_cap;
+  p.n_scans = n_scans; p.n_max = n_max; p.n_maps = n_maps; p.batch = L.batch; p.ev_cap = L.ev_cap;
   const unsigned ray_blocks = (unsigned)((n_max + kThreads - 1) / kThreads);
   const size_t cell_blocks = (cells + kThreads - 1) / kThreads;
   const unsigned sweep_blocks = (unsigned)(cell_blocks < 64 ? cell_blocks : 64);
   const unsigned apply_blocks = (unsigned)(cell_blocks < 148 * 8 ? cell_blocks : 148 * 8);
-  for (int s0 = 0; s0 < n_scans; s0 += L.batch) {
+  int b = 0;
+  for (int s0 = 0; s0 < n_scans; s0 += L.batch, ++b) {
+    const int k = b & 1;
+    int32_t* set = ws + k * L.set_stride;
+    p.planes = set + L.off_planes; p.bbox = set + L.off_bbox; p.ctl = set + L.off_ctl; p.events = set + L.off_events;
     p.s0 = s0;
     p.sb = n_scans - s0 < L.batch ? n_scans - s0 : L.batch;
+    if (b >= 2 && cudaStreamWaitEvent(st, streams->done[k], 0) != cudaSuccess) return B200ICP_ERR_CUDA;   // set k is free again
     ogm_reset_kernel<<<1, kThreads, 0, st>>>(p);
     ogm_count_kernel<<<dim3(ray_blocks, (unsigned)p.sb, (unsigned)n_maps), kThreads, 0, st>>>(p);
     ogm_classify_kernel<<<dim3(sweep_blocks, (unsigned)p.sb, (unsigned)n_maps), kThreads, 0, st>>>(p);
     ogm_event_kernel<<<dim3(ray_blocks, (unsigned)p.sb, (unsigned)n_maps), kThreads, 0, st>>>(p);
-    ogm_apply_kernel<<<dim3(apply_blocks, 1, (unsigned)n_maps), kThreads, 0, st>>>(p);
+    if (cudaEventRecord(streams->ready[k], st) != cudaSuccess) return B200ICP_ERR_CUDA;
+    if (cudaStreamWaitEvent(streams->aux, streams->ready[k], 0) != cudaSuccess) return B200ICP_ERR_CUDA;
+    ogm_apply_kernel<<<dim3(apply_blocks, 1, (unsigned)n_maps), kThreads, 0, streams->aux>>>(p);   // batches in order: one stream
+    if (cudaEventRecord(streams->done[k], streams->aux) != cudaSuccess) return B200ICP_ERR_CUDA;
   }
+  // join: the caller's stream continues after the last apply pass (the earlier ones precede it on aux)
+  if (cudaStreamWaitEvent(st, streams->done[(b - 1) & 1], 0) != cudaSuccess) return B200ICP_ERR_CUDA;
   return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
 }
 
