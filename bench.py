@@ -141,7 +141,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -420,7 +420,7 @@ def run_b200_arm(args):
             "sample": f"first {n_sample} pairs of pool 0, oracle port of modules/icp.py (scipy KDTree + numpy "
                       f"SVD), one process per core, slowest worker {r['seconds']:.1f} s",
             "mean_passes": r["mean_passes"]}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -447,6 +447,19 @@ def _measured_hbm():
         return 6650.0   # B200_PROFILING.md fallback
 
 
+_REAL_STDOUT = None
+
+
+def _emit(line):
+    text = json.dumps(line) + "\n"
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, text.encode())
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -458,6 +471,12 @@ def main():
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
                     help="multi-GPU pose exchange: fused peer stores (symmetric memory) or NCCL all-gather")
     args = ap.parse_args()
+    # stdout carries exactly ONE line (the JSON): libraries that print there (NCCL's version banner)
+    # are sent to stderr for the duration of the run; _emit() writes the line to the real stdout.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_b200_arm(args)
