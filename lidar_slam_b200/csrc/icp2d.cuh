@@ -301,30 +301,42 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
             if (!(sval > thr)) {
               ambiguous |= 1u << r;
             } else {
-              unsigned mask = 0;
-              const float4* tb = reinterpret_cast<const float4*>(t32 + blk * (2 * kBlockTargets));
-#pragma unroll 2
+              // fp32 filter on groups of four targets (packed math, bit-identical to the sweep):
+              // a group whose minimum is within the slack has all four members re-evaluated in
+              // float64 -- a superset of the candidates the slack admits, so the result is the
+              // same float64 argmin (lowest index on exact ties: groups and members ascend).
+              unsigned gmask = 0;
+              const ulonglong2* tb = reinterpret_cast<const ulonglong2*>(t32 + blk * (2 * kBlockTargets));
+              const f32x2 qxx = pack2(qx[r], qx[r]), qyy = pack2(qy[r], qy[r]);
+#pragma unroll
               for (int g = 0; g < kBlockTargets / 4; ++g) {
-                const float4 X = tb[2 * g], Y = tb[2 * g + 1];
-                if (dist2_2d(qx[r], qy[r], X.x, Y.x) <= thr) mask |= 1u << (4 * g);
-                if (dist2_2d(qx[r], qy[r], X.y, Y.y) <= thr) mask |= 2u << (4 * g);
-                if (dist2_2d(qx[r], qy[r], X.z, Y.z) <= thr) mask |= 4u << (4 * g);
-                if (dist2_2d(qx[r], qy[r], X.w, Y.w) <= thr) mask |= 8u << (4 * g);
+                const ulonglong2 X = tb[2 * g], Y = tb[2 * g + 1];
+                f32x2 dx = sub2(qxx, X.x), dy = sub2(qyy, Y.x);
+                const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
+                dx = sub2(qxx, X.y); dy = sub2(qyy, Y.y);
+                const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
+                float d0, d1, d2, d3;
+                unpack2(d01, d0, d1);
+                unpack2(d23, d2, d3);
+                if (fminf(fmin3(d0, d1, d2), d3) <= thr) gmask |= 1u << g;
               }
               const double2 s = s64[j];
               const double qdx = fma(r00, s.x, fma(r01, s.y, tx));
               const double qdy = fma(r10, s.x, fma(r11, s.y, ty));
               double bd = kInf;
               int bi = -1;
-              while (mask) {
-                const int i = __ffs(mask) - 1;
-                mask &= mask - 1;
-                const int idx = blk * kBlockTargets + i;
-                if (idx < nt) {
-                  const double2 t = t64[idx];
-                  const double ex = qdx - t.x, ey = qdy - t.y;
-                  const double d = ex * ex + ey * ey;
-                  if (d < bd) { bd = d; bi = idx; }
+              while (gmask) {
+                const int g = __ffs(gmask) - 1;
+                gmask &= gmask - 1;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const int idx = blk * kBlockTargets + 4 * g + u;
+                  if (idx < nt) {
+                    const double2 t = t64[idx];
+                    const double ex = qdx - t.x, ey = qdy - t.y;
+                    const double d = ex * ex + ey * ey;
+                    if (d < bd) { bd = d; bi = idx; }
+                  }
                 }
               }
               if (bi < 0) ambiguous |= 1u << r;  // cannot happen for finite data; be safe

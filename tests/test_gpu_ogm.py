@@ -153,3 +153,22 @@ def test_cells_with_long_mixed_event_lists(short_every):
     m.build_map(poses, meas)
     assert np.array_equal(m.grid_map_log_odds, o.log_odds)
     assert np.array_equal(m.grid_map, o.grid)
+
+
+def test_fine_grid_uses_short_batches():
+    """540 k cells: the count planes of one batch are capped at 48 MB, so a batch holds 23 scans
+    and 60 scans take three batches over two buffer sets; equals the oracle on every cell."""
+    from lidar_slam_b200 import ogm, synth
+    n = 60
+    poses = synth.make_trajectories(1, n, seed=11)[0]
+    scans, counts = synth.cast_scans(poses, seed=11)
+    scans, counts = scans.numpy(), counts.numpy()
+    meas = [scans[i, :counts[i]][::5] for i in range(n)]
+    res, box = 0.02, (9.0, 6.0, -9.0, -6.0)
+    o = oo.OgmOracle(res, *box)
+    o.build_map(poses, meas)
+    assert o.width * o.height * 4 * 64 > (48 << 20)
+    m = ogm.OccupancyGridMap(res, *box)
+    m.build_map(poses, meas)
+    assert np.array_equal(m.grid_map_log_odds, o.log_odds)
+    assert np.array_equal(m.grid_map, o.grid)
