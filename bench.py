@@ -358,6 +358,29 @@ def run_b200_arm(args):
     barrier()
     ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
 
+    # ---- timed region 3: the C ABI's host-buffer entry (numpy binding, no torch on the path) ----
+    # Every rank aligns its shard from pinned host arrays to host arrays; no pose exchange here
+    # (the caller of this entry is a single-process numpy program like the reference).
+    from lidar_slam_b200 import hostapi
+    host_np = [{k: v.numpy() for k, v in hp.items()} for hp in host]
+    host_res = None
+    for k in range(2):
+        hp = host_np[k % N_POOLS]
+        host_res = hostapi.run_icp_batch_host(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
+                                              max_iters=MAX_ITERS, stopping_thresh=STOP)
+    ref_T = results[1 % N_POOLS].T.cpu().numpy()
+    if not np.array_equal(host_res.T, ref_T):
+        raise RuntimeError("b200icp_run_host disagrees with the device entry on the bench batch")
+    barrier()
+    ev0.record()
+    for k in range(args.steps):
+        hp = host_np[k % N_POOLS]
+        hostapi.run_icp_batch_host(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
+                                   max_iters=MAX_ITERS, stopping_thresh=STOP)
+    ev1.record()
+    barrier()
+    ms_host_entry = max_over_ranks(ev0.elapsed_time(ev1))
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -403,7 +426,12 @@ def run_b200_arm(args):
                                 if peer is not None else "pack_poses + one NCCL all_gather_into_tensor of [B,4] f64 per step"),
                    "all_pairs_converged": ok},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                "ms_per_step": ms_e2e / args.steps},
+                "ms_per_step": ms_e2e / args.steps,
+                "c_abi_host_entry": {"value": world * B * args.steps / (ms_host_entry * 1e-3), "unit": UNIT,
+                                     "ms_per_step": ms_host_entry / args.steps,
+                                     "call": "b200icp_run_host via lidar_slam_b200.hostapi (pinned numpy arrays in, "
+                                             "numpy arrays out, no torch, no pose exchange)",
+                                     "d2h_bytes_per_step": B * (128 + 8 + 4 + 4)}},
         # icp2d_kernel per step, plus pack_poses_kernel when the exchange is not fused into it
         "gpu_launches": (1 if peer is not None else 2) * args.steps,
         "roofline": roofline,

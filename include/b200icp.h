@@ -111,6 +111,24 @@ int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans
                          int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
                          double* const* peer_pose_out, int n_peers, long long peer_row0);
 
+/* b200icp_run for callers that live in HOST memory, like the reference (numpy arrays): every
+ * pointer below is a host pointer (pinned or pageable), results included; the arguments mean
+ * what they mean for b200icp_run.  The library owns the device side: a grow-only arena on the
+ * current device, a copy stream and two compute streams.  The scan pool is streamed to the
+ * device in slices while the pair list runs in chunks (consecutive pairs (i, i-1), the shape of
+ * modules/localization.py:112-130, overlap copy and compute; any other pair list is correct,
+ * it just waits for more of the pool).  With dim == 2, initial transforms that leave the z = 0
+ * plane send the whole batch through the general kernel on z-padded scans, as the reference's
+ * lifting does (icp.py:153-156).  Synchronous: outputs are filled on return.  err_out, iters_out,
+ * status_out and corr_out may be NULL.  Calls on one device are serialised.
+ * b200icp_host_release frees the arena of the current device. */
+int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                     const int32_t* pairs, const double* init, const double* epsilon,
+                     const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                     double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                     int32_t* corr_out);
+int b200icp_host_release(void);
+
 /* One exact nearest-neighbour pass, exposed on its own for tests and for the
  * roofline measurement.  Replaces get_correspondences / KDTree.query
  * (modules/icp.py:29-41 with :161) for a batch of (query set, target set) pairs

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200icp.so")
-SOURCES = ["api.cu", "voxel.cu", "scan_build.cu", "ogm.cu", "texture.cu"]
+SOURCES = ["api.cu", "host_api.cu", "voxel.cu", "scan_build.cu", "ogm.cu", "texture.cu"]
 HEADERS = ["icp_common.cuh", "icp2d.cuh", "icp3d.cuh", "kabsch3.cuh",
            os.path.join("..", "..", "include", "b200icp.h")]
 NVCC_FLAGS = [

@@ -185,6 +185,16 @@ def test_c_abi_argument_validation_without_a_device():
     assert lib.b200icp_run(one, one, 1, 2, 2, one, one, one, one, 1, -1, 1e-4, one, one, one, one, null, one, 256, null) == -1
     assert lib.b200icp_run_exchange(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
                                     null, null, 3, 0) == -1                      # peers announced but no array
+    # host-buffer entry: bad arguments, the empty pair list (nothing to do), and no device here
+    assert lib.b200icp_run_host(null, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null) == -1
+    assert lib.b200icp_run_host(one, one, 1, 3, 3, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null) == -1  # odd row
+    assert lib.b200icp_run_host(one, one, 1, 2, 2, one, one, one, one, 0, 5, 1e-4, one, one, one, one, null) == 0
+    import torch
+    if not torch.cuda.is_available():
+        z = np.zeros((1, 2, 2)); c = np.ones(1, dtype=np.int32); pr = np.zeros((1, 2), dtype=np.int32)
+        from lidar_slam_b200 import hostapi
+        with pytest.raises(RuntimeError):
+            hostapi.run_icp_batch_host(z, c, pr)
     assert lib.b200icp_run_exchange(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
                                     null, one, 17, 0) == -1                      # more than 16 peers
     assert lib.b200icp_scans_from_ranges(one, 1, 1081, one, one, 0.1, 30.0, 0.1, 0.0, one, one, 1081, null) == -1   # odd n_max
@@ -205,3 +215,15 @@ def test_c_abi_argument_validation_without_a_device():
             ogm.OccupancyGridMap(0.1, 1, 1, -1, -1)
         with pytest.raises(RuntimeError, match="no CPU fallback"):
             texture_mapping.TexturePainter(10, 10, 0.1, 0, 0, np.eye(4), np.eye(3))
+
+
+def test_host_binding_does_not_import_torch():
+    """The numpy binding of the host-buffer entry is usable without torch (what a maintainer of the
+    numpy-only reference would bind)."""
+    import subprocess
+    import sys
+    code = ("import sys; import lidar_slam_b200.hostapi as h; import lidar_slam_b200 as p; "
+            "p.pack_scans_numpy; assert 'torch' not in sys.modules, 'torch was imported'; print('ok')")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and out.stdout.strip() == "ok", out.stderr
