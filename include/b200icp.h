@@ -5,10 +5,12 @@
  * replaces.  Plain pointers and sizes only; no torch / C++ types.
  *
  * Ownership: the caller allocates and frees EVERY buffer (device memory unless
- * stated otherwise), including the workspace.  The library keeps no global
- * state, never allocates device memory, and is re-entrant.  All launches are
- * asynchronous on the given CUDA stream (pass a cudaStream_t cast to void*;
- * NULL = the legacy default stream).  Functions return 0 or a negative
+ * stated otherwise), including the workspace; the entries never allocate device
+ * memory and are re-entrant.  All launches are asynchronous on the given CUDA
+ * stream (pass a cudaStream_t cast to void*; NULL = the legacy default stream).
+ * Two documented exceptions: b200icp_run_host takes HOST pointers and owns a
+ * per-device arena and streams (freed by b200icp_host_release), and
+ * b200icp_ogm_build keeps one auxiliary stream per device.  Functions return 0 or a negative
  * B200ICP_ERR_* code; per-pair anomalies are reported in `status_out`, never
  * as a call failure, because the reference does not raise on them either.
  */

@@ -96,3 +96,13 @@ def test_host_entry_statuses_and_argument_errors():
     with pytest.raises(ValueError):
         hostapi.run_icp_batch_host(b["scans"], counts, pairs, init[:2])
     hostapi.release()
+
+
+def test_plain_c_caller_recovers_a_known_motion(tmp_path):
+    """tests/c/abi_smoke.c: a C99 program (no Python, no CUDA headers) aligns two scans through
+    b200icp_run_host and checks the transform it gets back."""
+    import subprocess
+    from test_host import _build_c_caller
+    exe = _build_c_caller(tmp_path)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr

@@ -227,3 +227,28 @@ def test_host_binding_does_not_import_torch():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=120)
     assert out.returncode == 0 and out.stdout.strip() == "ok", out.stderr
+
+
+def _build_c_caller(tmp_path):
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    from lidar_slam_b200 import build
+    build.build()
+    exe = str(tmp_path / "abi_smoke")
+    libdir = os.path.join(root, "lidar_slam_b200")
+    cmd = ["gcc", "-std=c99", "-O1", "-Wall", "-Werror", "-I", os.path.join(root, "include"),
+           os.path.join(root, "tests", "c", "abi_smoke.c"), "-o", exe, "-L", libdir, "-lb200icp", "-lm",
+           "-Wl,-rpath," + libdir]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    return exe
+
+
+def test_header_is_plain_c_and_a_c_program_links(tmp_path):
+    """include/b200icp.h compiles as C99 with -Wall -Werror, a C caller links against the library,
+    and without a device the call fails loudly (exit code 2 = the library's error string path)."""
+    import subprocess
+    exe = _build_c_caller(tmp_path)
+    if not torch.cuda.is_available():
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+        assert out.returncode == 2 and "no sm_100" in out.stdout, (out.returncode, out.stdout)
