@@ -265,3 +265,42 @@ def test_yaw_sweep_best_of_24_matches_oracle():
         assert rot < 1e-8 and trans < 1e-8, (k, rot, trans)
     assert round(float(err.min()), 3) == round(min(
         orc.run_icp_info(src, tgt, inits[k], epsilon=1e-3, normalize_error=True)[1] for k in range(24)), 3)
+
+
+@pytest.mark.parametrize("n_src", [5, 31, 32, 33, 255, 257, 544, 1024, 1280, 2047, 2048, 2050])
+def test_full_icp_across_row_layouts_and_kernel_boundaries(n_src):
+    """Source sizes that exercise every row layout of the planar kernel (whole rows per warp, 0-7
+    shared left-over rows, the <2,4>, <4,4>, <5,8> and <8,8> variants) and the hand-over to the
+    general kernel above 2048 points: passes, poses, errors and matches equal the oracle."""
+    eng = _engine()
+    from oracle import icp_oracle as orc
+    rng = np.random.default_rng(n_src)
+    ang = np.sort(rng.uniform(-2.2, 2.2, n_src + 40))
+    rad = 4.0 + 1.5 * np.sin(3 * ang) + 0.8 * np.sign(np.sin(7 * ang))
+    tgt = np.stack([rad * np.cos(ang), rad * np.sin(ang)], 1) + rng.normal(scale=2e-3, size=(n_src + 40, 2))
+    th, t = 0.012, np.array([0.02, -0.015])
+    R = np.array([[np.cos(th), -np.sin(th)], [np.sin(th), np.cos(th)]])
+    src = (tgt[20:20 + n_src] - t) @ R + rng.normal(scale=2e-3, size=(n_src, 2))
+    T, err, corr = eng.run_icp(src, tgt, epsilon=1e-9, max_iters=40, return_error=True, return_correspondences=True)
+    To, eo, co, po = orc.run_icp_info(src, tgt, np.eye(4), epsilon=1e-9, max_iters=40)
+    rot, trans = _pose_delta(T, To)
+    assert rot < TIGHT and trans < TIGHT, (rot, trans)
+    assert err == pytest.approx(eo, rel=1e-9)
+    assert np.array_equal(corr, co)
+
+
+def test_reflection_branch_on_device_matches_oracle():
+    """A mirrored source makes det(cross-covariance) < 0: the reference's SVD solution is then a
+    REFLECTION of the plane (icp.py:62-67 on planar data); the device's closed
+    form takes the same branch and reports R[2,2] = -1."""
+    eng = _engine()
+    from oracle import icp_oracle as orc
+    rng = np.random.default_rng(8)
+    n = 300
+    s = rng.choice([-1.0, 1.0], n)
+    tgt = np.stack([0.1 * np.arange(n), 0.01 * s * (1 + rng.random(n))], 1)      # a zig-zag along the x axis
+    src = tgt * np.array([1.0, -1.0]) + rng.normal(scale=1e-4, size=tgt.shape)  # mirrored: point i still matches i
+    T, err = eng.run_icp(src, tgt, epsilon=1e-12, max_iters=3, return_error=True)
+    To, eo, _, po = orc.run_icp_info(src, tgt, np.eye(4), epsilon=1e-12, max_iters=3)
+    assert To[2, 2] < 0                                # the oracle (== reference) did reflect
+    assert np.abs(T - To).max() < 1e-9 and err == pytest.approx(eo, rel=1e-9)
