@@ -618,9 +618,21 @@ int b200icp_ogm_build(float* log_odds, int width, int height, double res, double
   std::lock_guard<std::mutex> lock(enqueue_mutex);
   OgmStreams* streams = ogm_streams();
   if (!streams) return B200ICP_ERR_CUDA;
-  for (int k = 0; k < 2; ++k)
-    if (cudaMemsetAsync(ws + k * L.set_stride + L.off_planes, 0, (size_t)n_maps * L.batch * cells * sizeof(int32_t), st) != cudaSuccess)
-      return B200ICP_ERR_CUDA;
+  // zero the count planes this call will use (the apply pass leaves them zeroed again): all of a
+  // set when the scans fill a batch, otherwise only the leading planes of every map (update_map
+  // with one scan then clears one plane, not sixty-four)
+  const int sets_used = n_scans > L.batch ? 2 : 1;
+  const int planes_used = n_scans < L.batch ? n_scans : L.batch;
+  for (int k = 0; k < sets_used; ++k) {
+    int32_t* planes = ws + k * L.set_stride + L.off_planes;
+    if (planes_used == L.batch) {
+      if (cudaMemsetAsync(planes, 0, (size_t)n_maps * L.batch * cells * sizeof(int32_t), st) != cudaSuccess) return B200ICP_ERR_CUDA;
+    } else {
+      for (int m = 0; m < n_maps; ++m)
+        if (cudaMemsetAsync(planes + (size_t)m * L.batch * cells, 0, (size_t)planes_used * cells * sizeof(int32_t), st) != cudaSuccess)
+          return B200ICP_ERR_CUDA;
+    }
+  }
   OgmParams p{};
   p.log_odds = log_odds; p.width = width; p.height = height; p.res = res; p.min_x = min_x; p.min_y = min_y;
   p.poses = poses; p.cs = cos_sin; p.scans = scans; p.counts = counts;
