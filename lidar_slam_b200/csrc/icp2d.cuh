@@ -28,6 +28,18 @@
 
 namespace b200icp {
 
+#ifdef B200ICP_PHASE_PROFILE
+// developer instrumentation: cycles per phase, summed over warp 0 of every CTA into queue[16 + 2*i]
+#define PHASE_DECL long long ph_t = clock64(); long long ph_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define PHASE(i) do { const long long now_ = clock64(); ph_acc[i] += now_ - ph_t; ph_t = now_; } while (0)
+#define PHASE_FLUSH do { if (tid == 0) for (int i_ = 0; i_ < 8; ++i_) \
+    atomicAdd(reinterpret_cast<unsigned long long*>(p.queue) + 8 + i_, (unsigned long long)ph_acc[i_]); } while (0)
+#else
+#define PHASE_DECL
+#define PHASE(i) do { } while (0)
+#define PHASE_FLUSH do { } while (0)
+#endif
+
 constexpr int kSums2d = 9;    // sum qx qy px py qxpx qxpy qypx qypy sse   (shifted by origin)
 constexpr int kRed2d = 17;    // + min/max of qx qy px py
 
@@ -120,9 +132,11 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     fence_mbar_init();
   }
   uint32_t parity = 0;
+  PHASE_DECL
 
   for (;;) {
     __syncthreads();  // previous pair fully consumed; mbarrier initialised
+    PHASE(7);
     if (tid == 0) *s_pair = (int)atomicAdd(p.queue, 1u);
     __syncthreads();
     const int pair = *s_pair;
@@ -207,6 +221,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     ox /= (double)nt; oy /= (double)nt;  // shift origin for the one-pass covariance
     __syncthreads();                     // red[] is reused by the passes below
 
+    PHASE(0);
     const double epsilon = p.nearest_only ? 0.0 : p.epsilon[pair];
     const bool normalize = p.nearest_only ? false : (p.normalize[pair] != 0);
     const int nblk = (nt + kBlockTargets - 1) / kBlockTargets;
@@ -271,6 +286,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
             if (r < cnt) part[((ph * R + r) * W + warp) * 32 + lane] = make_uint2(best[r], second[r]);
         }
       }
+      PHASE(1);
       if (extra > 0) {
         __syncthreads();        // the shared rows' partial results are complete
         if (warp < extra) {     // merge the W partial top-2 lists of shared row `warp` into slot `base`
@@ -286,6 +302,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
             if (r == base) { best[r] = b; second[r] = s2; }
         }
       }
+      PHASE(2);
       if (nr > 0) {
         // 3. exact resolution in float64
         unsigned ambiguous = 0;
@@ -376,6 +393,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
             if (lane == src_lane) corr[r] = (bi == 0x7fffffff) ? 0 : bi;
           }
         }
+        PHASE(3);
         // 4. float64 sums over this thread's matched pairs
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -411,6 +429,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           }
         }
       }
+      PHASE(4);
       // exchange: one shared-memory round per pass, double-buffered by pass parity
       double* slot = red + (size_t)(passes & 1) * W * kRed2d;
       if (lane == 0) {
@@ -442,6 +461,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       }
       passes += 1;
 
+      PHASE(5);
       // 5. error of this pass (before the update), solve, compose, stop tests
       double err = tot[8];
       if (normalize) {
@@ -481,6 +501,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         r00 = n00; r01 = n01; r10 = n10; r11 = n11; tx = ntx; ty = nty; zs *= dz;
         status = stop_test(st, err, epsilon, p.max_iters, p.stopping_thresh);
       }
+      PHASE(6);
       if (status >= 0) {
         if (tid == 0) {
           if (p.T_out) {
@@ -508,6 +529,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       }
     }
   }
+  PHASE_FLUSH;
 }
 
 }  // namespace b200icp
