@@ -106,3 +106,26 @@ def test_plain_c_caller_recovers_a_known_motion(tmp_path):
     exe = _build_c_caller(tmp_path)
     out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
+
+
+def test_host_entry_from_two_threads():
+    """ctypes drops the GIL during the call; the library serialises calls on one device (shared
+    arena and streams).  Two threads, different batches, results equal the single-threaded ones."""
+    import threading
+    from lidar_slam_b200 import hostapi
+    a, b = _batch(600, 21), _batch(2500, 22)
+    want_a = hostapi.run_icp_batch_host(a["scans"], a["counts"], a["pairs"], a["init"], epsilon=1e-3)
+    want_b = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
+    got = {}
+
+    def work(name, d, reps):
+        for _ in range(reps):
+            got[name] = hostapi.run_icp_batch_host(d["scans"], d["counts"], d["pairs"], d["init"], epsilon=1e-3)
+
+    ts = [threading.Thread(target=work, args=("a", a, 6)), threading.Thread(target=work, args=("b", b, 3))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert np.array_equal(got["a"].T, want_a.T) and np.array_equal(got["a"].iters, want_a.iters)
+    assert np.array_equal(got["b"].T, want_b.T) and np.array_equal(got["b"].iters, want_b.iters)
