@@ -129,3 +129,25 @@ def test_host_entry_from_two_threads():
         t.join()
     assert np.array_equal(got["a"].T, want_a.T) and np.array_equal(got["a"].iters, want_a.iters)
     assert np.array_equal(got["b"].T, want_b.T) and np.array_equal(got["b"].iters, want_b.iters)
+
+
+def test_integration_md_numpy_binding_snippet_runs():
+    """The ctypes binding printed in INTEGRATION.md section 3a is executed as it stands (only the
+    library path is made absolute) and must reproduce the package's own result."""
+    import os
+    import re
+    from lidar_slam_b200 import _lib, hostapi
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "INTEGRATION.md")).read()
+    blocks = re.findall(r"```python\n(.*?)```", text, flags=re.S)
+    snippet = [b for b in blocks if "b200icp_run_host" in b and "def run_icp_pairs" in b]
+    assert len(snippet) == 1
+    code = snippet[0].replace('"libb200icp.so"', repr(_lib.LIB_PATH))
+    ns = {}
+    exec(compile(code, "INTEGRATION.md:3a", "exec"), ns)
+    b = _batch(40, 5)
+    z_ts = [b["scans"][i, :b["counts"][i]] for i in range(b["scans"].shape[0])]
+    pairs = [tuple(p) for p in b["pairs"]]
+    T, err = ns["run_icp_pairs"](z_ts, pairs, b["init"], epsilon=1e-3)
+    want = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
+    assert np.array_equal(T, want.T) and np.array_equal(err, want.error)
