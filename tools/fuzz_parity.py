@@ -8,6 +8,7 @@ from lidar_slam_b200 import hostapi
 from oracle import icp_oracle as orc
 
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
+big = len(sys.argv) > 3 and sys.argv[3] == "big"      # clouds of 2100..6000 points: the general kernel, 2-D and 3-D
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
 t_end = time.time() + budget
 n_cases = n_pairs = 0
@@ -17,6 +18,8 @@ while time.time() < t_end:
     n_scans = int(rng.integers(2, 6))
     clouds = []
     base_n = int(rng.choice([rng.integers(24, 70), rng.integers(70, 600), rng.integers(600, 2300)]))   # tiny clouds: rank-deficient fits, see DESIGN.md section 2
+    if big:
+        base_n = int(rng.integers(2100, 6000))
     if dim == 2:
         ang = np.sort(rng.uniform(-2.3, 2.3, base_n + 50))
         rad = 3.0 + rng.uniform(0.5, 3.0) * np.sin(rng.integers(1, 6) * ang) + rng.uniform(0, 1.5) * np.sign(np.sin(9 * ang))
