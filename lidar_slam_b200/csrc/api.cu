@@ -36,10 +36,21 @@ DeviceInfo device_info() {
   return d;
 }
 
-template <int R, int W, int MINB>
-int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
-  auto kern = icp2d_kernel<R, W, MINB>;
-  const Smem2dLayout L = smem2d_layout(p.n_max, W);
+// B200ICP_SWEEP=exhaustive selects the sweep that evaluates every (source, target) candidate
+// (same results; kept for A/B timing and as the FP32-issue-rate figure of the inner loop).
+// Default: the block-pruned sweep (icp2d.cuh).
+bool prune_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200ICP_SWEEP");
+    return !(e && (e[0] == 'e' || e[0] == 'E'));
+  }();
+  return on;
+}
+
+template <int R, int W, int MINB, bool PRUNE>
+int launch2d_variant(const RunParams& p, cudaStream_t stream, int sms) {
+  auto kern = icp2d_kernel<R, W, MINB, PRUNE>;
+  const Smem2dLayout L = smem2d_layout(p.n_max, W, PRUNE, R);
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
     return B200ICP_ERR_CUDA;
   int per_sm = 0;
@@ -49,6 +60,11 @@ int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
   const int grid = (int)(p.n_pairs < resident ? p.n_pairs : resident);
   kern<<<grid, W * 32, L.total, stream>>>(p);
   return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+template <int R, int W, int MINB>
+int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
+  return prune_enabled() ? launch2d_variant<R, W, MINB, true>(p, stream, sms)
+                         : launch2d_variant<R, W, MINB, false>(p, stream, sms);
 }
 
 int launch3d(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, int sms) {

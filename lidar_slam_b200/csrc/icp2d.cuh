@@ -45,9 +45,11 @@ constexpr int kRed2d = 17;    // + min/max of qx qy px py
 
 struct Smem2dLayout {
   int np;          // padded point capacity (multiple of 32)
-  size_t off_t64, off_s64, off_t32, off_red, off_part, off_ctl, total;
+  size_t off_t64, off_s64, off_t32, off_red, off_part, off_bb, off_rb, off_ctl, total;
 };
-__host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps) {
+// prune = true: the block-pruned sweep (bounding boxes of the target blocks and of the source rows
+// instead of the shared-row exchange area).
+__host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps, bool prune, int rows_per_thread) {
   Smem2dLayout L;
   L.np = ((n_max + 31) / 32) * 32;
   size_t o = 0;
@@ -55,7 +57,9 @@ __host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps) {
   L.off_s64 = o; o += (size_t)L.np * 16;
   L.off_t32 = o; o += (size_t)L.np * 8;
   L.off_red = o; o += (size_t)2 * warps * kRed2d * 8;
-  L.off_part = o; o += (size_t)(warps - 1) * warps * 32 * 8;   // shared rows: (best, second) per warp and lane
+  L.off_part = o; o += prune ? 0 : (size_t)(warps - 1) * warps * 32 * 8;   // shared rows: (best, second) per warp and lane
+  L.off_bb = o; o += prune ? (size_t)64 * 16 : 0;                           // target-block boxes (xmin, xmax, ymin, ymax)
+  L.off_rb = o; o += prune ? (size_t)warps * rows_per_thread * 16 : 0;      // source-row boxes, per warp and row slot
   L.off_ctl = o; o += 64;
   L.total = o;
   return L;
@@ -69,9 +73,40 @@ __device__ __forceinline__ float2 target32(const float* t32, int i) {
   return make_float2(g[0], g[4]);
 }
 
-// The NN sweep for NR source points per thread (rows of 32 sources per warp).
+// One 32-target block of the NN sweep for NR source points per thread (rows of 32 sources per warp).
 // Per 4 candidates: 2x(FADD2, FADD2, FMUL2, FFMA2) + 2 FMNMX3, i.e. 8 FP32-pipe issue slots
 // carrying the 16 algorithmic lane-instructions, plus 0.5 ALU slot per candidate.
+template <int NR, int RMAX>
+__device__ __forceinline__ void sweep_block(const ulonglong2* tp, int b, const f32x2 (&qxx)[NR], const f32x2 (&qyy)[NR],
+                                            unsigned (&best)[RMAX], unsigned (&second)[RMAX]) {
+  float bm[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) bm[r] = __int_as_float(0x7f800000);
+#pragma unroll
+  for (int i = 0; i < kBlockTargets / 4; ++i) {
+    const ulonglong2 X = tp[b * (kBlockTargets / 2) + 2 * i];
+    const ulonglong2 Y = tp[b * (kBlockTargets / 2) + 2 * i + 1];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      f32x2 dx = sub2(qxx[r], X.x), dy = sub2(qyy[r], Y.x);
+      const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
+      dx = sub2(qxx[r], X.y); dy = sub2(qyy[r], Y.y);
+      const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
+      float d0, d1, d2, d3;
+      unpack2(d01, d0, d1);
+      unpack2(d23, d2, d3);
+      bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const unsigned pk = (__float_as_uint(bm[r]) & 0xffffffc0u) | (unsigned)b;
+    second[r] = min(second[r], max(best[r], pk));
+    best[r] = min(best[r], pk);
+  }
+}
+
+// Exhaustive sweep over the blocks [blk_lo, blk_hi).
 template <int NR, int RMAX>
 __device__ __forceinline__ void sweep2d(const float* t32, int blk_lo, int blk_hi, const float (&qx)[RMAX],
                                         const float (&qy)[RMAX], unsigned (&best)[RMAX],
@@ -80,44 +115,110 @@ __device__ __forceinline__ void sweep2d(const float* t32, int blk_lo, int blk_hi
 #pragma unroll
   for (int r = 0; r < NR; ++r) { qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); }
   const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(t32);
-  for (int b = blk_lo; b < blk_hi; ++b) {
-    float bm[NR];
-#pragma unroll
-    for (int r = 0; r < NR; ++r) bm[r] = __int_as_float(0x7f800000);
-#pragma unroll
-    for (int i = 0; i < kBlockTargets / 4; ++i) {
-      const ulonglong2 X = tp[b * (kBlockTargets / 2) + 2 * i];
-      const ulonglong2 Y = tp[b * (kBlockTargets / 2) + 2 * i + 1];
-#pragma unroll
-      for (int r = 0; r < NR; ++r) {
-        f32x2 dx = sub2(qxx[r], X.x), dy = sub2(qyy[r], Y.x);
-        const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
-        dx = sub2(qxx[r], X.y); dy = sub2(qyy[r], Y.y);
-        const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
-        float d0, d1, d2, d3;
-        unpack2(d01, d0, d1);
-        unpack2(d23, d2, d3);
-        bm[r] = fmin3(fmin3(bm[r], d0, d1), d2, d3);
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < NR; ++r) {
-      const unsigned pk = (__float_as_uint(bm[r]) & 0xffffffc0u) | (unsigned)b;
-      second[r] = min(second[r], max(best[r], pk));
-      best[r] = min(best[r], pk);
-    }
-  }
+  for (int b = blk_lo; b < blk_hi; ++b) sweep_block<NR, RMAX>(tp, b, qxx, qyy, best, second);
 }
 
-template <int R, int W, int MINB>
+// ---------------------------------------------------------------------------------------------
+// Block-pruned sweep.  Exactly the same matches as the exhaustive sweep, with the blocks that
+// cannot matter left out.
+//
+// Every target block b has a bounding box B_b of its fp32 points, every source row r (32 queries
+// of one warp) a bounding box Q_r of its fp32 queries.  lb(Q_r, B_b) is computed with the SAME
+// operations as a candidate distance (FADD, FADD, FMUL, FFMA on the per-axis gaps); rounding to
+// nearest is monotone, so lb(Q_r, B_b) <= d32(q, t) for every q in the row and every t in the
+// block -- no error term is needed.
+//   1. seeds: per row the two blocks of smallest lb are swept first (REDUX.MIN over the lanes,
+//      lane l evaluates blocks l and l + 32).
+//   2. bound: thr(q) = candidate_threshold(best(q)) is the value the resolution phase will use to
+//      decide which targets are candidates and whether a second block is ambiguous; it is
+//      monotone in best(q), and best(q) only decreases, so thr_now(q) >= thr_final(q).  A block
+//      with lb(Q_r, B_b) > max_q thr_now(q) for every row of the warp therefore holds no target
+//      with d32 <= thr_final(q) for any query: it is neither the best block, nor a reason for
+//      the ambiguity fallback, nor does it hold a candidate.  Such blocks are skipped.
+//   3. the other blocks are swept as usual.
+// The (best, second) lists then cover a superset of all blocks with a minimum <= thr_final, which
+// is all the resolution reads; the float64 result is the exhaustive one (same tie rule).
+// Returns the number of blocks swept (for the evaluated-candidate counter).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float box_lb(const float4 q, const float4 b) {   // boxes: (xmin, xmax, ymin, ymax)
+  const float ex = fmaxf(fmaxf(__fsub_rn(b.x, q.y), __fsub_rn(q.x, b.y)), 0.f);
+  const float ey = fmaxf(fmaxf(__fsub_rn(b.z, q.w), __fsub_rn(q.z, b.w)), 0.f);
+  return __fmaf_rn(ex, ex, __fmul_rn(ey, ey));
+}
+
+template <int NR, int RMAX>
+__device__ __forceinline__ int sweep2d_pruned(const float* t32, const float4* bb, const float4* rb, int nblk,
+                                              unsigned vmask, float tmax, float trunc_rel, const float (&qx)[RMAX],
+                                              const float (&qy)[RMAX], unsigned (&best)[RMAX],
+                                              unsigned (&second)[RMAX]) {
+  const int lane = threadIdx.x & 31;
+  const float kInfF = __int_as_float(0x7f800000);
+  const bool has0 = lane < nblk, has1 = lane + 32 < nblk;
+  const float4 far_box = make_float4(kInfF, kInfF, kInfF, kInfF);
+  const float4 bb0 = has0 ? bb[lane] : far_box;
+  const float4 bb1 = has1 ? bb[lane + 32] : far_box;
+  f32x2 qxx[NR], qyy[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) { qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); }
+  const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(t32);
+
+  // 1. seeds
+  unsigned long long seeds = 0;
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const float4 q = rb[r];
+    unsigned k0 = has0 ? ((__float_as_uint(box_lb(q, bb0)) & 0xffffffc0u) | (unsigned)lane) : 0xffffffffu;
+    unsigned k1 = has1 ? ((__float_as_uint(box_lb(q, bb1)) & 0xffffffc0u) | (unsigned)(lane + 32)) : 0xffffffffu;
+    const unsigned f = __reduce_min_sync(0xffffffffu, min(k0, k1));
+    if (k0 == f) k0 = 0xffffffffu;
+    if (k1 == f) k1 = 0xffffffffu;
+    const unsigned s = __reduce_min_sync(0xffffffffu, min(k0, k1));
+    if (f != 0xffffffffu) seeds |= 1ull << (f & 63u);
+    if (s != 0xffffffffu) seeds |= 1ull << (s & 63u);
+  }
+  int swept = __popcll(seeds);
+  for (unsigned long long m = seeds; m;) {
+    const int b = __ffsll((long long)m) - 1;
+    m &= m - 1;
+    sweep_block<NR, RMAX>(tp, b, qxx, qyy, best, second);
+  }
+
+  // 2. which of the other blocks can still hold a candidate of any query of these rows
+  bool need0 = false, need1 = false;
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const float bval = __uint_as_float(best[r] & 0xffffffc0u);
+    const float a_bound = fmaxf(fabsf(qx[r]), fabsf(qy[r])) * (1.0f + 4.0f * kU) + tmax;
+    const float thr = candidate_threshold(bval, a_bound, trunc_rel);
+    const unsigned bound = __reduce_max_sync(0xffffffffu, ((vmask >> r) & 1u) ? __float_as_uint(thr) : 0u);
+    const float4 q = rb[r];
+    need0 = need0 || !(__float_as_uint(box_lb(q, bb0)) > bound);
+    need1 = need1 || !(__float_as_uint(box_lb(q, bb1)) > bound);
+  }
+  unsigned long long rest = (unsigned long long)__ballot_sync(0xffffffffu, need0 && has0) |
+                            ((unsigned long long)__ballot_sync(0xffffffffu, need1 && has1) << 32);
+  rest &= ~seeds;
+  swept += __popcll(rest);
+  // 3. the remaining blocks
+  for (unsigned long long m = rest; m;) {
+    const int b = __ffsll((long long)m) - 1;
+    m &= m - 1;
+    sweep_block<NR, RMAX>(tp, b, qxx, qyy, best, second);
+  }
+  return swept;
+}
+
+template <int R, int W, int MINB, bool PRUNE>
 __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const Smem2dLayout L = smem2d_layout(p.n_max, W);
+  const Smem2dLayout L = smem2d_layout(p.n_max, W, PRUNE, R);
   double2* t64 = reinterpret_cast<double2*>(smem_raw + L.off_t64);
   double2* s64 = reinterpret_cast<double2*>(smem_raw + L.off_s64);
   float* t32 = reinterpret_cast<float*>(smem_raw + L.off_t32);
   double* red = reinterpret_cast<double*>(smem_raw + L.off_red);
   uint2* part = reinterpret_cast<uint2*>(smem_raw + L.off_part);
+  float4* bb = reinterpret_cast<float4*>(smem_raw + L.off_bb);
+  float4* rb = reinterpret_cast<float4*>(smem_raw + L.off_rb) + (threadIdx.x >> 5) * R;
   uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw + L.off_ctl);
   int* s_pair = reinterpret_cast<int*>(smem_raw + L.off_ctl + 16);
 
@@ -210,6 +311,17 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     cy = warp_sum(cy);
     if (lane == 0) { red[warp * 3 + 0] = (double)amax; red[warp * 3 + 1] = cx; red[warp * 3 + 2] = cy; }
     __syncthreads();
+    if constexpr (PRUNE) {   // bounding boxes of the real fp32 targets of every 32-target block
+      const float kInfF = __int_as_float(0x7f800000);
+      for (int b = warp; b < (nt + kBlockTargets - 1) / kBlockTargets; b += W) {
+        const int i = b * kBlockTargets + lane;
+        float2 v = target32(t32, i);
+        const bool real = i < nt;
+        const float xlo = warp_minf(real ? v.x : kInfF), xhi = warp_maxf(real ? v.x : -kInfF);
+        const float ylo = warp_minf(real ? v.y : kInfF), yhi = warp_maxf(real ? v.y : -kInfF);
+        if (lane == 0) bb[b] = make_float4(xlo, xhi, ylo, yhi);
+      }
+    }
     float tmax = 0.f;
     double ox = 0.0, oy = 0.0;
 #pragma unroll
@@ -238,6 +350,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     auto row_of = [&](int r) { return r < base ? warp * base + r : base * W + warp; };
     StopState st{0.0, 0, 0};
     int passes = 0;
+    unsigned tiles = 0;     // (32-source row) x (32-target block) tiles this warp swept for this pair
 
     for (;;) {  // ------------------------------ one ICP pass ------------------------
       double acc[kRed2d];
@@ -251,6 +364,44 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 
       float qx[R], qy[R];
       unsigned best[R], second[R];
+      if constexpr (PRUNE) {
+        // 1+2. transform, row boxes and the block-pruned fp32 sweep over this warp's rows
+        // (slot `base` holds the warp's left-over row, if it has one).
+        unsigned vmask = 0;
+        const float kInfF = __int_as_float(0x7f800000);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int j = row_of(r) * 32 + lane;
+          qx[r] = 0.f; qy[r] = 0.f;
+          best[r] = 0xffffffffu; second[r] = 0xffffffffu;
+          const bool v = r < nr && j < ns;
+          if (v) {
+            const double2 s = s64[j];
+            qx[r] = (float)fma(r00, s.x, fma(r01, s.y, tx));
+            qy[r] = (float)fma(r10, s.x, fma(r11, s.y, ty));
+            vmask |= 1u << r;
+          }
+          if (r < nr) {   // warp-uniform
+            const float xlo = warp_minf(v ? qx[r] : kInfF), xhi = warp_maxf(v ? qx[r] : -kInfF);
+            const float ylo = warp_minf(v ? qy[r] : kInfF), yhi = warp_maxf(v ? qy[r] : -kInfF);
+            if (lane == 0) rb[r] = make_float4(xlo, xhi, ylo, yhi);
+          }
+        }
+        __syncwarp();
+        int swept = 0;
+        switch (nr) {
+#define B200ICP_SWEEP_CASE(N) \
+  case N:                     \
+    if constexpr (N <= R) swept = sweep2d_pruned<N, R>(t32, bb, rb, nblk, vmask, tmax, kTruncRel, qx, qy, best, second); \
+    break;
+          B200ICP_SWEEP_CASE(1) B200ICP_SWEEP_CASE(2) B200ICP_SWEEP_CASE(3) B200ICP_SWEEP_CASE(4)
+          B200ICP_SWEEP_CASE(5) B200ICP_SWEEP_CASE(6) B200ICP_SWEEP_CASE(7) B200ICP_SWEEP_CASE(8)
+#undef B200ICP_SWEEP_CASE
+          default: break;
+        }
+        tiles += (unsigned)(swept * nr);
+        __syncwarp();   // rb[] is rewritten by the next pass
+      } else {
       // 1+2. transform and fp32 sweep: first the shared rows (chunks of <= R rows, this warp's
       // share of the target blocks, results to shared memory), last this warp's own rows.
       for (int ph = 0; ph <= n_shared_chunks; ++ph) {
@@ -285,9 +436,11 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           for (int r = 0; r < R; ++r)
             if (r < cnt) part[((ph * R + r) * W + warp) * 32 + lane] = make_uint2(best[r], second[r]);
         }
+        tiles += (unsigned)(cnt * (blk_hi - blk_lo));
+      }
       }
       PHASE(1);
-      if (extra > 0) {
+      if (!PRUNE && extra > 0) {
         __syncthreads();        // the shared rows' partial results are complete
         if (warp < extra) {     // merge the W partial top-2 lists of shared row `warp` into slot `base`
           unsigned b = 0xffffffffu, s2 = 0xffffffffu;
@@ -503,6 +656,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       }
       PHASE(6);
       if (status >= 0) {
+        if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(p.queue) + 1, (unsigned long long)tiles);
         if (tid == 0) {
           if (p.T_out) {
             double* T = p.T_out + (size_t)pair * 16;

@@ -116,6 +116,11 @@ __device__ __forceinline__ float warp_maxf(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
+__device__ __forceinline__ float warp_minf(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
 // (distance, index) minimum; exact ties go to the lower index.
 __device__ __forceinline__ void warp_argmin(double& d, int& i) {
 #pragma unroll

@@ -219,6 +219,8 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     nbytes = ctypes.c_size_t()
     _lib.check(lib.b200icp_workspace_bytes(n_pairs, n_max, dim, ctypes.byref(nbytes)), "b200icp_workspace_bytes")
     ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
+    global _last_workspace
+    _last_workspace = ws
 
     def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax, ws=ws, row0=0):
         with torch.cuda.device(dev):
@@ -257,6 +259,18 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     else:
         launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
     return IcpBatchResult(T, err, iters, status, corr)
+
+
+_last_workspace = None
+
+
+def swept_tiles() -> int:
+    """(32-source row x 32-target block) tiles the planar kernel swept in the most recent
+    single-launch run_icp_batch call (workspace bytes 8..15, include/b200icp.h); x 1024 = candidate
+    distance evaluations including padding lanes.  Synchronises."""
+    if _last_workspace is None:
+        raise RuntimeError("no run_icp_batch call yet")
+    return int(_last_workspace[8:16].cpu().numpy().view(np.uint64)[0])
 
 
 def pack_poses(T: torch.Tensor, error: Optional[torch.Tensor] = None) -> torch.Tensor:
