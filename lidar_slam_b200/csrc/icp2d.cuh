@@ -146,65 +146,69 @@ __device__ __forceinline__ float box_lb(const float4 q, const float4 b) {   // b
   return __fmaf_rn(ex, ex, __fmul_rn(ey, ey));
 }
 
-template <int NR, int RMAX>
-__device__ __forceinline__ int sweep2d_pruned(const float* t32, const float4* bb, const float4* rb, int nblk,
-                                              unsigned vmask, float tmax, float trunc_rel, const float (&qx)[RMAX],
-                                              const float (&qy)[RMAX], unsigned (&best)[RMAX],
-                                              unsigned (&second)[RMAX]) {
+// fp32 warp reductions in one instruction (CREDUX.MIN/MAX.F32, sm_100a); NaN operands are ignored.
+__device__ __forceinline__ float redux_minf(float v) {
+  float r;
+  asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float redux_maxf(float v) {
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+
+// One row (32 queries, one per lane; `valid` = this lane holds a real source point).
+__device__ __forceinline__ int sweep_row_pruned(const float* t32, const float4* bb, int nblk, bool valid, float qx,
+                                                float qy, float tmax, float trunc_rel, unsigned& best_out,
+                                                unsigned& second_out) {
   const int lane = threadIdx.x & 31;
   const float kInfF = __int_as_float(0x7f800000);
   const bool has0 = lane < nblk, has1 = lane + 32 < nblk;
-  const float4 far_box = make_float4(kInfF, kInfF, kInfF, kInfF);
-  const float4 bb0 = has0 ? bb[lane] : far_box;
-  const float4 bb1 = has1 ? bb[lane + 32] : far_box;
-  f32x2 qxx[NR], qyy[NR];
-#pragma unroll
-  for (int r = 0; r < NR; ++r) { qxx[r] = pack2(qx[r], qx[r]); qyy[r] = pack2(qy[r], qy[r]); }
+  // row box and this lane's two block bounds
+  const float4 q = make_float4(redux_minf(valid ? qx : kInfF), redux_maxf(valid ? qx : -kInfF),
+                               redux_minf(valid ? qy : kInfF), redux_maxf(valid ? qy : -kInfF));
+  unsigned lb0 = 0xffffffffu, lb1 = 0xffffffffu;
+  if (has0) lb0 = __float_as_uint(box_lb(q, bb[lane]));
+  if (has1) lb1 = __float_as_uint(box_lb(q, bb[lane + 32]));
+  // 1. seeds: the two blocks of smallest bound
+  unsigned k0 = has0 ? ((lb0 & 0xffffffc0u) | (unsigned)lane) : 0xffffffffu;
+  unsigned k1 = has1 ? ((lb1 & 0xffffffc0u) | (unsigned)(lane + 32)) : 0xffffffffu;
+  const unsigned f = __reduce_min_sync(0xffffffffu, min(k0, k1));
+  if (k0 == f) k0 = 0xffffffffu;
+  if (k1 == f) k1 = 0xffffffffu;
+  const unsigned s = __reduce_min_sync(0xffffffffu, min(k0, k1));
+  unsigned long long m = 0;
+  if (f != 0xffffffffu) m |= 1ull << (f & 63u);
+  if (s != 0xffffffffu) m |= 1ull << (s & 63u);
+
+  f32x2 qxx[1], qyy[1];
+  unsigned best[1] = {0xffffffffu}, second[1] = {0xffffffffu};
+  qxx[0] = pack2(qx, qx); qyy[0] = pack2(qy, qy);
   const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(t32);
-
-  // 1. seeds
-  unsigned long long seeds = 0;
-#pragma unroll
-  for (int r = 0; r < NR; ++r) {
-    const float4 q = rb[r];
-    unsigned k0 = has0 ? ((__float_as_uint(box_lb(q, bb0)) & 0xffffffc0u) | (unsigned)lane) : 0xffffffffu;
-    unsigned k1 = has1 ? ((__float_as_uint(box_lb(q, bb1)) & 0xffffffc0u) | (unsigned)(lane + 32)) : 0xffffffffu;
-    const unsigned f = __reduce_min_sync(0xffffffffu, min(k0, k1));
-    if (k0 == f) k0 = 0xffffffffu;
-    if (k1 == f) k1 = 0xffffffffu;
-    const unsigned s = __reduce_min_sync(0xffffffffu, min(k0, k1));
-    if (f != 0xffffffffu) seeds |= 1ull << (f & 63u);
-    if (s != 0xffffffffu) seeds |= 1ull << (s & 63u);
+  unsigned long long done = 0;
+  int swept = 0;
+#pragma unroll 1
+  for (int phase = 0; phase < 2; ++phase) {
+    swept += __popcll(m);
+    done |= m;
+    while (m) {
+      const int b = __ffsll((long long)m) - 1;
+      m &= m - 1;
+      sweep_block<1, 1>(tp, b, qxx, qyy, best, second);
+    }
+    if (phase == 0) {
+      // 2. the other blocks that can still hold a candidate of any query of this row
+      const float bval = __uint_as_float(best[0] & 0xffffffc0u);
+      const float a_bound = fmaxf(fabsf(qx), fabsf(qy)) * (1.0f + 4.0f * kU) + tmax;
+      const float thr = candidate_threshold(bval, a_bound, trunc_rel);
+      const unsigned bound = __reduce_max_sync(0xffffffffu, valid ? __float_as_uint(thr) : 0u);
+      m = ((unsigned long long)__ballot_sync(0xffffffffu, has0 && !(lb0 > bound)) |
+           ((unsigned long long)__ballot_sync(0xffffffffu, has1 && !(lb1 > bound)) << 32)) & ~done;
+    }
   }
-  int swept = __popcll(seeds);
-  for (unsigned long long m = seeds; m;) {
-    const int b = __ffsll((long long)m) - 1;
-    m &= m - 1;
-    sweep_block<NR, RMAX>(tp, b, qxx, qyy, best, second);
-  }
-
-  // 2. which of the other blocks can still hold a candidate of any query of these rows
-  bool need0 = false, need1 = false;
-#pragma unroll
-  for (int r = 0; r < NR; ++r) {
-    const float bval = __uint_as_float(best[r] & 0xffffffc0u);
-    const float a_bound = fmaxf(fabsf(qx[r]), fabsf(qy[r])) * (1.0f + 4.0f * kU) + tmax;
-    const float thr = candidate_threshold(bval, a_bound, trunc_rel);
-    const unsigned bound = __reduce_max_sync(0xffffffffu, ((vmask >> r) & 1u) ? __float_as_uint(thr) : 0u);
-    const float4 q = rb[r];
-    need0 = need0 || !(__float_as_uint(box_lb(q, bb0)) > bound);
-    need1 = need1 || !(__float_as_uint(box_lb(q, bb1)) > bound);
-  }
-  unsigned long long rest = (unsigned long long)__ballot_sync(0xffffffffu, need0 && has0) |
-                            ((unsigned long long)__ballot_sync(0xffffffffu, need1 && has1) << 32);
-  rest &= ~seeds;
-  swept += __popcll(rest);
-  // 3. the remaining blocks
-  for (unsigned long long m = rest; m;) {
-    const int b = __ffsll((long long)m) - 1;
-    m &= m - 1;
-    sweep_block<NR, RMAX>(tp, b, qxx, qyy, best, second);
-  }
+  best_out = best[0];
+  second_out = second[0];
   return swept;
 }
 
@@ -365,42 +369,115 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       float qx[R], qy[R];
       unsigned best[R], second[R];
       if constexpr (PRUNE) {
-        // 1+2. transform, row boxes and the block-pruned fp32 sweep over this warp's rows
-        // (slot `base` holds the warp's left-over row, if it has one).
-        unsigned vmask = 0;
-        const float kInfF = __int_as_float(0x7f800000);
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
+        // One rolled loop over this warp's rows: transform, pruned fp32 sweep, exact resolution,
+        // sums.  (A rolled loop keeps the kernel small: the exhaustive variant's five-row unrolled
+        // phases no longer pay once the sweep is pruned -- instruction fetch was the top stall.)
+#pragma unroll 1
+        for (int r = 0; r < nr; ++r) {
           const int j = row_of(r) * 32 + lane;
-          qx[r] = 0.f; qy[r] = 0.f;
-          best[r] = 0xffffffffu; second[r] = 0xffffffffu;
-          const bool v = r < nr && j < ns;
+          const bool v = j < ns;
+          double qdx = 0.0, qdy = 0.0;
           if (v) {
             const double2 s = s64[j];
-            qx[r] = (float)fma(r00, s.x, fma(r01, s.y, tx));
-            qy[r] = (float)fma(r10, s.x, fma(r11, s.y, ty));
-            vmask |= 1u << r;
+            qdx = fma(r00, s.x, fma(r01, s.y, tx));
+            qdy = fma(r10, s.x, fma(r11, s.y, ty));
           }
-          if (r < nr) {   // warp-uniform
-            const float xlo = warp_minf(v ? qx[r] : kInfF), xhi = warp_maxf(v ? qx[r] : -kInfF);
-            const float ylo = warp_minf(v ? qy[r] : kInfF), yhi = warp_maxf(v ? qy[r] : -kInfF);
-            if (lane == 0) rb[r] = make_float4(xlo, xhi, ylo, yhi);
+          const float fqx = (float)qdx, fqy = (float)qdy;
+          unsigned bst, snd;
+          tiles += (unsigned)sweep_row_pruned(t32, bb, nblk, v, fqx, fqy, tmax, kTruncRel, bst, snd);
+          // 3. exact resolution in float64
+          int c = -1;
+          bool amb = false;
+          const float a_bound = fmaxf(fabsf(fqx), fabsf(fqy)) * (1.0f + 4.0f * kU) + tmax;
+          const float thr = candidate_threshold(__uint_as_float(bst & 0xffffffc0u), a_bound, kTruncRel);
+          if (v) {
+            const float sval = __uint_as_float(snd & 0xffffffc0u);
+            if (!(sval > thr)) {
+              amb = true;
+            } else {
+              const int blk = (int)(bst & 63u);
+              unsigned gmask = 0;
+              const ulonglong2* tb = reinterpret_cast<const ulonglong2*>(t32 + blk * (2 * kBlockTargets));
+              const f32x2 qxx = pack2(fqx, fqx), qyy = pack2(fqy, fqy);
+#pragma unroll
+              for (int g = 0; g < kBlockTargets / 4; ++g) {
+                const ulonglong2 X = tb[2 * g], Y = tb[2 * g + 1];
+                f32x2 dx = sub2(qxx, X.x), dy = sub2(qyy, Y.x);
+                const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
+                dx = sub2(qxx, X.y); dy = sub2(qyy, Y.y);
+                const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
+                float d0, d1, d2, d3;
+                unpack2(d01, d0, d1);
+                unpack2(d23, d2, d3);
+                if (fminf(fmin3(d0, d1, d2), d3) <= thr) gmask |= 1u << g;
+              }
+              double bd = kInf;
+              while (gmask) {
+                const int g = __ffs(gmask) - 1;
+                gmask &= gmask - 1;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const int idx = blk * kBlockTargets + 4 * g + u;
+                  if (idx < nt) {
+                    const double2 t = t64[idx];
+                    const double ex = qdx - t.x, ey = qdy - t.y;
+                    const double d = ex * ex + ey * ey;
+                    if (d < bd) { bd = d; c = idx; }
+                  }
+                }
+              }
+              if (c < 0) amb = true;  // cannot happen for finite data; be safe
+            }
           }
+          // 3b. rare: a second block is within the slack -> the warp scans all targets
+          unsigned vote = __ballot_sync(0xffffffffu, amb);
+          while (vote) {
+            const int src_lane = __ffs(vote) - 1;
+            vote &= vote - 1;
+            const float fx = __shfl_sync(0xffffffffu, fqx, src_lane);
+            const float fy = __shfl_sync(0xffffffffu, fqy, src_lane);
+            const float thr_s = __shfl_sync(0xffffffffu, thr, src_lane);
+            const double sdx = __shfl_sync(0xffffffffu, qdx, src_lane);
+            const double sdy = __shfl_sync(0xffffffffu, qdy, src_lane);
+            double bd = kInf;
+            int bi = 0x7fffffff;
+            for (int i = lane; i < nt; i += 32) {
+              const float2 t = target32(t32, i);
+              // !(d > thr) also admits NaN so that non-finite data still yields an index
+              if (!(dist2_2d(fx, fy, t.x, t.y) > thr_s)) {
+                const double2 td = t64[i];
+                const double ex = sdx - td.x, ey = sdy - td.y;
+                const double d = ex * ex + ey * ey;
+                if (d < bd || bi == 0x7fffffff) { bd = d; bi = i; }
+              }
+            }
+            warp_argmin(bd, bi);
+            if (lane == src_lane) c = (bi == 0x7fffffff) ? 0 : bi;
+          }
+          // 4. float64 sums over the matched pairs
+          if (v) {
+            const double2 t = t64[c];
+            const double ux = qdx - ox, uy = qdy - oy, vx = t.x - ox, vy = t.y - oy;
+            acc[0] += ux; acc[1] += uy; acc[2] += vx; acc[3] += vy;
+            acc[4] = fma(ux, vx, acc[4]); acc[5] = fma(ux, vy, acc[5]);
+            acc[6] = fma(uy, vx, acc[6]); acc[7] = fma(uy, vy, acc[7]);
+            const double ex = qdx - t.x, ey = qdy - t.y;
+            acc[8] += ex * ex + ey * ey;
+            if (normalize) {
+              acc[9] = fmin(acc[9], qdx);   acc[10] = fmax(acc[10], qdx);
+              acc[11] = fmin(acc[11], qdy); acc[12] = fmax(acc[12], qdy);
+              acc[13] = fmin(acc[13], t.x); acc[14] = fmax(acc[14], t.x);
+              acc[15] = fmin(acc[15], t.y); acc[16] = fmax(acc[16], t.y);
+            }
+            if (p.nearest_only && p.dist2_out)
+              p.dist2_out[(size_t)pair * p.n_max + j] = ex * ex + ey * ey;
+          }
+          // the row's match enters the register queue at the top: after the loop row r sits in slot R - nr + r
+#pragma unroll
+          for (int i = 0; i + 1 < R; ++i) corr[i] = corr[i + 1];
+          corr[R - 1] = c;
         }
-        __syncwarp();
-        int swept = 0;
-        switch (nr) {
-#define B200ICP_SWEEP_CASE(N) \
-  case N:                     \
-    if constexpr (N <= R) swept = sweep2d_pruned<N, R>(t32, bb, rb, nblk, vmask, tmax, kTruncRel, qx, qy, best, second); \
-    break;
-          B200ICP_SWEEP_CASE(1) B200ICP_SWEEP_CASE(2) B200ICP_SWEEP_CASE(3) B200ICP_SWEEP_CASE(4)
-          B200ICP_SWEEP_CASE(5) B200ICP_SWEEP_CASE(6) B200ICP_SWEEP_CASE(7) B200ICP_SWEEP_CASE(8)
-#undef B200ICP_SWEEP_CASE
-          default: break;
-        }
-        tiles += (unsigned)(swept * nr);
-        __syncwarp();   // rb[] is rewritten by the next pass
+        PHASE(1);
       } else {
       // 1+2. transform and fp32 sweep: first the shared rows (chunks of <= R rows, this warp's
       // share of the target blocks, results to shared memory), last this warp's own rows.
@@ -457,6 +534,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       }
       PHASE(2);
       if (nr > 0) {
+        if constexpr (!PRUNE) {
         // 3. exact resolution in float64
         unsigned ambiguous = 0;
 #pragma unroll
@@ -572,6 +650,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
               p.dist2_out[(size_t)pair * p.n_max + j] = ex * ex + ey * ey;
           }
         }
+        }  // !PRUNE
 #pragma unroll
         for (int k = 0; k < kSums2d; ++k) acc[k] = warp_sum(acc[k]);
         if (normalize) {
@@ -674,8 +753,9 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           int* out = p.corr_out + (size_t)pair * p.n_max;
 #pragma unroll
           for (int r = 0; r < R; ++r) {
-            const int j = row_of(r) * 32 + lane;
-            if (r < nr && j < ns) out[j] = corr[r];
+            const int rr = PRUNE ? r - (R - nr) : r;       // pruned variant: register queue, see above
+            const int j = row_of(rr) * 32 + lane;
+            if (rr >= 0 && rr < nr && j < ns) out[j] = corr[r];
           }
           for (int j = ns + tid; j < p.n_max; j += W * 32) out[j] = -1;
         }
