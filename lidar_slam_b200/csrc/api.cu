@@ -39,12 +39,9 @@ DeviceInfo device_info() {
 // B200ICP_SWEEP=exhaustive selects the sweep that evaluates every (source, target) candidate
 // (same results; kept for A/B timing and as the FP32-issue-rate figure of the inner loop).
 // Default: the block-pruned sweep (icp2d.cuh).
-bool prune_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("B200ICP_SWEEP");
-    return !(e && (e[0] == 'e' || e[0] == 'E'));
-  }();
-  return on;
+bool prune_enabled() {   // read at every launch, so a caller can switch between two launches
+  const char* e = getenv("B200ICP_SWEEP");
+  return !(e && (e[0] == 'e' || e[0] == 'E'));
 }
 
 template <int R, int W, int MINB, bool PRUNE>

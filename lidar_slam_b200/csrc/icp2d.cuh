@@ -106,6 +106,36 @@ __device__ __forceinline__ void sweep_block(const ulonglong2* tp, int b, const f
   }
 }
 
+// One block for ONE row, keeping the minima of its eight groups of four targets: when the block
+// becomes the row's best block they are saved in gbest[], so that the resolution can tell which
+// groups hold candidates without evaluating the block's 32 distances a second time.
+__device__ __forceinline__ void sweep_block_row(const ulonglong2* tp, int b, f32x2 qxx, f32x2 qyy, unsigned& best,
+                                                unsigned& second, float (&gbest)[kBlockTargets / 4]) {
+  float gm[kBlockTargets / 4];
+#pragma unroll
+  for (int i = 0; i < kBlockTargets / 4; ++i) {
+    const ulonglong2 X = tp[b * (kBlockTargets / 2) + 2 * i];
+    const ulonglong2 Y = tp[b * (kBlockTargets / 2) + 2 * i + 1];
+    f32x2 dx = sub2(qxx, X.x), dy = sub2(qyy, Y.x);
+    const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
+    dx = sub2(qxx, X.y); dy = sub2(qyy, Y.y);
+    const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
+    float d0, d1, d2, d3;
+    unpack2(d01, d0, d1);
+    unpack2(d23, d2, d3);
+    gm[i] = fminf(fmin3(d0, d1, d2), d3);
+  }
+  static_assert(kBlockTargets == 32, "eight groups per block");
+  const float bm = fminf(fmin3(fmin3(fmin3(gm[0], gm[1], gm[2]), gm[3], gm[4]), gm[5], gm[6]), gm[7]);
+  const unsigned pk = (__float_as_uint(bm) & 0xffffffc0u) | (unsigned)b;
+  if (pk < best) {
+#pragma unroll
+    for (int i = 0; i < kBlockTargets / 4; ++i) gbest[i] = gm[i];
+  }
+  second = min(second, max(best, pk));
+  best = min(best, pk);
+}
+
 // Exhaustive sweep over the blocks [blk_lo, blk_hi).
 template <int NR, int RMAX>
 __device__ __forceinline__ void sweep2d(const float* t32, int blk_lo, int blk_hi, const float (&qx)[RMAX],
@@ -161,7 +191,8 @@ __device__ __forceinline__ float redux_maxf(float v) {
 // One row (32 queries, one per lane; `valid` = this lane holds a real source point).
 __device__ __forceinline__ int sweep_row_pruned(const float* t32, const float4* bb, int nblk, bool valid, float qx,
                                                 float qy, float tmax, float trunc_rel, unsigned& best_out,
-                                                unsigned& second_out) {
+                                                unsigned& second_out, float& thr_out,
+                                                float (&gbest)[kBlockTargets / 4]) {
   const int lane = threadIdx.x & 31;
   const float kInfF = __int_as_float(0x7f800000);
   const bool has0 = lane < nblk, has1 = lane + 32 < nblk;
@@ -182,33 +213,34 @@ __device__ __forceinline__ int sweep_row_pruned(const float* t32, const float4* 
   if (f != 0xffffffffu) m |= 1ull << (f & 63u);
   if (s != 0xffffffffu) m |= 1ull << (s & 63u);
 
-  f32x2 qxx[1], qyy[1];
-  unsigned best[1] = {0xffffffffu}, second[1] = {0xffffffffu};
-  qxx[0] = pack2(qx, qx); qyy[0] = pack2(qy, qy);
+  unsigned best = 0xffffffffu, second = 0xffffffffu;
+  const f32x2 qxx = pack2(qx, qx), qyy = pack2(qy, qy);
   const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(t32);
   unsigned long long done = 0;
   int swept = 0;
+  const float a_bound = fmaxf(fabsf(qx), fabsf(qy)) * (1.0f + 4.0f * kU) + tmax;
+  float thr;
 #pragma unroll 1
-  for (int phase = 0; phase < 2; ++phase) {
+  for (int phase = 0;; ++phase) {
     swept += __popcll(m);
     done |= m;
     while (m) {
       const int b = __ffsll((long long)m) - 1;
       m &= m - 1;
-      sweep_block<1, 1>(tp, b, qxx, qyy, best, second);
+      sweep_block_row(tp, b, qxx, qyy, best, second, gbest);
     }
-    if (phase == 0) {
-      // 2. the other blocks that can still hold a candidate of any query of this row
-      const float bval = __uint_as_float(best[0] & 0xffffffc0u);
-      const float a_bound = fmaxf(fabsf(qx), fabsf(qy)) * (1.0f + 4.0f * kU) + tmax;
-      const float thr = candidate_threshold(bval, a_bound, trunc_rel);
-      const unsigned bound = __reduce_max_sync(0xffffffffu, valid ? __float_as_uint(thr) : 0u);
-      m = ((unsigned long long)__ballot_sync(0xffffffffu, has0 && !(lb0 > bound)) |
-           ((unsigned long long)__ballot_sync(0xffffffffu, has1 && !(lb1 > bound)) << 32)) & ~done;
-    }
+    // the threshold the resolution uses (final once no further block is swept)
+    thr = candidate_threshold(__uint_as_float(best & 0xffffffc0u), a_bound, trunc_rel);
+    if (phase == 1) break;
+    // 2. the other blocks that can still hold a candidate of any query of this row
+    const unsigned bound = __reduce_max_sync(0xffffffffu, valid ? __float_as_uint(thr) : 0u);
+    m = ((unsigned long long)__ballot_sync(0xffffffffu, has0 && !(lb0 > bound)) |
+         ((unsigned long long)__ballot_sync(0xffffffffu, has1 && !(lb1 > bound)) << 32)) & ~done;
+    if (m == 0) break;
   }
-  best_out = best[0];
-  second_out = second[0];
+  thr_out = thr;
+  best_out = best;
+  second_out = second;
   return swept;
 }
 
@@ -230,6 +262,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
   const int lane = tid & 31;
   const int warp = tid >> 5;
   constexpr float kTruncRel = 1.52587890625e-5f;  // 2^-16 >= the 6 truncated mantissa bits (2^-17)
+  const float kInfF32 = __int_as_float(0x7f800000);
   const double kInf = __longlong_as_double(0x7ff0000000000000LL);
 
   if (tid == 0) {
@@ -384,33 +417,27 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           }
           const float fqx = (float)qdx, fqy = (float)qdy;
           unsigned bst, snd;
-          tiles += (unsigned)sweep_row_pruned(t32, bb, nblk, v, fqx, fqy, tmax, kTruncRel, bst, snd);
+          float thr;
+          float gbest[kBlockTargets / 4];
+#pragma unroll
+          for (int g = 0; g < kBlockTargets / 4; ++g) gbest[g] = kInfF32;
+          tiles += (unsigned)sweep_row_pruned(t32, bb, nblk, v, fqx, fqy, tmax, kTruncRel, bst, snd, thr, gbest);
           // 3. exact resolution in float64
           int c = -1;
           bool amb = false;
-          const float a_bound = fmaxf(fabsf(fqx), fabsf(fqy)) * (1.0f + 4.0f * kU) + tmax;
-          const float thr = candidate_threshold(__uint_as_float(bst & 0xffffffc0u), a_bound, kTruncRel);
           if (v) {
             const float sval = __uint_as_float(snd & 0xffffffc0u);
             if (!(sval > thr)) {
               amb = true;
             } else {
               const int blk = (int)(bst & 63u);
+              // groups of four targets whose minimum (kept from the sweep) is within the slack: all
+              // four members are re-evaluated in float64 -- a superset of the candidates the slack
+              // admits, so the result is the float64 argmin (lowest index on exact ties).
               unsigned gmask = 0;
-              const ulonglong2* tb = reinterpret_cast<const ulonglong2*>(t32 + blk * (2 * kBlockTargets));
-              const f32x2 qxx = pack2(fqx, fqx), qyy = pack2(fqy, fqy);
 #pragma unroll
-              for (int g = 0; g < kBlockTargets / 4; ++g) {
-                const ulonglong2 X = tb[2 * g], Y = tb[2 * g + 1];
-                f32x2 dx = sub2(qxx, X.x), dy = sub2(qyy, Y.x);
-                const f32x2 d01 = fma2(dx, dx, mul2(dy, dy));
-                dx = sub2(qxx, X.y); dy = sub2(qyy, Y.y);
-                const f32x2 d23 = fma2(dx, dx, mul2(dy, dy));
-                float d0, d1, d2, d3;
-                unpack2(d01, d0, d1);
-                unpack2(d23, d2, d3);
-                if (fminf(fmin3(d0, d1, d2), d3) <= thr) gmask |= 1u << g;
-              }
+              for (int g = 0; g < kBlockTargets / 4; ++g)
+                if (gbest[g] <= thr) gmask |= 1u << g;
               double bd = kInf;
               while (gmask) {
                 const int g = __ffs(gmask) - 1;
@@ -673,23 +700,21 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         }
       }
       __syncthreads();
+      // Column k of the W partial rows is reduced by lane k (same order as a sequential sum over
+      // the warps), then every lane fetches the totals it needs by shuffle.
       double tot[kRed2d];
-#pragma unroll
-      for (int k = 0; k < kRed2d; ++k) tot[k] = slot[k];
-#pragma unroll
-      for (int w = 1; w < W; ++w) {
-#pragma unroll
-        for (int k = 0; k < kSums2d; ++k) tot[k] += slot[w * kRed2d + k];
-      }
-      if (normalize) {
+      {
+        const int kcol = lane < kRed2d ? lane : kRed2d - 1;
+        double col = slot[kcol];
 #pragma unroll
         for (int w = 1; w < W; ++w) {
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            tot[kSums2d + 2 * k] = fmin(tot[kSums2d + 2 * k], slot[w * kRed2d + kSums2d + 2 * k]);
-            tot[kSums2d + 2 * k + 1] = fmax(tot[kSums2d + 2 * k + 1], slot[w * kRed2d + kSums2d + 2 * k + 1]);
-          }
+          const double o = slot[w * kRed2d + kcol];
+          col = kcol < kSums2d ? col + o : ((kcol & 1) ? fmin(col, o) : fmax(col, o));   // 9, 11, ..: minima
         }
+#pragma unroll
+        for (int k = 0; k < kSums2d; ++k) tot[k] = __shfl_sync(0xffffffffu, col, k);
+#pragma unroll
+        for (int k = kSums2d; k < kRed2d; ++k) tot[k] = normalize ? __shfl_sync(0xffffffffu, col, k) : 0.0;
       }
       passes += 1;
 
