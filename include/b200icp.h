@@ -54,7 +54,11 @@ const char* b200icp_error_string(int code);
 
 /* Bytes of device workspace b200icp_run / b200icp_nearest need for this problem size: the work
  * queue (256 B) and, for the general kernel (dim 3, or dim 2 with n_max > 2048), one fp32 copy of
- * a target per resident cluster.  Concurrent launches need separate workspaces. */
+ * a target per resident cluster.  Concurrent launches need separate workspaces.
+ * After a run of the planar kernel, bytes 8..15 of the workspace hold (uint64) the number of
+ * (32 source points x 32 target points) tiles whose candidate distances were really evaluated --
+ * the block-pruned sweep skips the tiles that provably hold no candidate (same results as the
+ * exhaustive sweep; environment B200ICP_SWEEP=exhaustive, read at every launch, turns pruning off). */
 int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out);
 
 /* Batched point-to-point ICP.  Replaces, for every pair b independently,

@@ -122,6 +122,16 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (p.n_max <= 256) return launch2d<2, 4, 8>(p, stream, d.sms);
     if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
     if (p.n_max <= 1280) {
+      if (prune_enabled()) {
+        int v = 0;
+        if (const char* e = getenv("B200ICP_VARIANT")) v = atoi(e);      // developer A/B of CTA shapes
+        switch (v) {
+          case 1: return launch2d_variant<7, 6, 4, true>(p, stream, d.sms);
+          case 2: return launch2d_variant<6, 7, 4, true>(p, stream, d.sms);
+          case 3: return launch2d_variant<7, 6, 3, true>(p, stream, d.sms);
+          default: break;
+        }
+      }
       return launch2d<5, 8, 3>(p, stream, d.sms);
     }
     return launch2d<8, 8, 2>(p, stream, d.sms);

@@ -89,6 +89,37 @@ def test_fp32_slack_bounds_the_fp64_distance(dim, scale):
         assert np.all(np.abs(d32.astype(np.float64) - d64) <= 0.5 * bound)    # the documented factor 2
 
 
+def test_box_lower_bound_never_exceeds_the_fp32_candidate_distance():
+    """The pruned sweep (icp2d.cuh, box_lb) skips a target block when lb(row box, block box) exceeds
+    the candidate threshold.  lb is computed with the candidate distance's own fp32 operations on the
+    per-axis gaps; rounding to nearest is monotone, so lb <= d32(q, t) for EVERY q in the row box and
+    t in the block box, with no error term.  Emulated here in numpy float32 (FMA in float64 rounded
+    once), on boxes that overlap, touch and lie far apart, at small and large coordinates."""
+    f32 = np.float32
+
+    def fma32(a, b, c):        # one rounding, like FFMA (exact product and sum fit float64 for fp32 inputs)
+        return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(f32)
+
+    def d32(qx, qy, tx, ty):
+        dx, dy = (qx - tx).astype(f32), (qy - ty).astype(f32)
+        return fma32(dx, dx, (dy * dy).astype(f32))
+
+    rng = np.random.default_rng(5)
+    for scale, spread in ((1.0, 0.3), (30.0, 2.0), (30.0, 1e-3), (4000.0, 50.0), (1e-3, 1e-4)):
+        for _ in range(200):
+            q = (rng.uniform(-scale, scale, 2) + rng.normal(scale=spread, size=(32, 2))).astype(f32)
+            t = (rng.uniform(-scale, scale, 2) + rng.normal(scale=spread, size=(32, 2))).astype(f32)
+            if rng.random() < 0.3:
+                t = (q[rng.integers(0, 32, 32)] + rng.normal(scale=spread * 1e-3, size=(32, 2))).astype(f32)
+            qb = (q[:, 0].min(), q[:, 0].max(), q[:, 1].min(), q[:, 1].max())
+            tb = (t[:, 0].min(), t[:, 0].max(), t[:, 1].min(), t[:, 1].max())
+            ex = np.maximum(np.maximum(f32(tb[0]) - f32(qb[1]), f32(qb[0]) - f32(tb[1])), f32(0)).astype(f32)
+            ey = np.maximum(np.maximum(f32(tb[2]) - f32(qb[3]), f32(qb[2]) - f32(tb[3])), f32(0)).astype(f32)
+            lb = fma32(np.array(ex), np.array(ex), np.array((ey * ey), dtype=f32))
+            d = d32(q[:, None, 0], q[:, None, 1], t[None, :, 0], t[None, :, 1])
+            assert lb <= d.min(), (scale, spread, float(lb), float(d.min()))
+
+
 def test_host_kabsch3_matches_lapack(tmp_path):
     """kabsch3.cuh (compiled for the host with g++) against the reference's SVD recipe."""
     src = tmp_path / "hk.cpp"
