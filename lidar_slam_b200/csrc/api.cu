@@ -122,16 +122,6 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (p.n_max <= 256) return launch2d<2, 4, 8>(p, stream, d.sms);
     if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
     if (p.n_max <= 1280) {
-      if (prune_enabled()) {
-        int v = 0;
-        if (const char* e = getenv("B200ICP_VARIANT")) v = atoi(e);      // developer A/B of CTA shapes
-        switch (v) {
-          case 1: return launch2d_variant<7, 6, 4, true>(p, stream, d.sms);
-          case 2: return launch2d_variant<6, 7, 4, true>(p, stream, d.sms);
-          case 3: return launch2d_variant<7, 6, 3, true>(p, stream, d.sms);
-          default: break;
-        }
-      }
       return launch2d<5, 8, 3>(p, stream, d.sms);
     }
     return launch2d<8, 8, 2>(p, stream, d.sms);
@@ -202,8 +192,10 @@ static int run_common(const double* scans, const int32_t* counts, int n_scans, i
                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                       int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
-                      double* const* peer_pose_out, int n_peers, long long peer_row0) {
+                      double* const* peer_pose_out, int n_peers, long long peer_row0,
+                      const unsigned int* ready_scans = nullptr) {
   if (!init || !epsilon || !normalize || !T_out || max_iters < 0) return B200ICP_ERR_BAD_ARG;
+  if (ready_scans && uses_general_kernel(n_max, dim)) return B200ICP_ERR_BAD_ARG;   // planar kernel only
   if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && !peer_pose_out) || peer_row0 < 0)
     return B200ICP_ERR_BAD_ARG;
   RunParams p{};
@@ -213,6 +205,7 @@ static int run_common(const double* scans, const int32_t* counts, int n_scans, i
   p.T_out = T_out; p.err_out = err_out; p.iters_out = iters_out; p.status_out = status_out;
   p.corr_out = corr_out; p.dist2_out = nullptr; p.nearest_only = 0;
   p.n_peers = n_peers; p.peer_row0 = peer_row0;
+  p.ready_scans = ready_scans;
   for (int k = 0; k < n_peers; ++k) {
     if (!peer_pose_out[k] || (reinterpret_cast<uintptr_t>(peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
     p.peer_out[k] = peer_pose_out[k];
@@ -239,6 +232,18 @@ int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans
   return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
                     stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
                     workspace_bytes, stream, peer_pose_out, n_peers, peer_row0);
+}
+
+int b200icp_run_gated(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                      const int32_t* pairs, const double* init, const double* epsilon,
+                      const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                      double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                      int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
+                      const unsigned int* ready_scans) {
+  if (!ready_scans) return B200ICP_ERR_BAD_ARG;
+  return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
+                    stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
+                    workspace_bytes, stream, nullptr, 0, 0, ready_scans);
 }
 
 int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,

@@ -9,6 +9,11 @@
 // to the device in slices while the pair list runs in chunks: before chunk c starts, the prefix
 // of the pool its pairs reference is resident (consecutive pairs (i, i-1) need the pool in
 // order, so copy and compute overlap; arbitrary pair lists simply wait for more of the pool).
+// Planar batches take the GATED path instead of chunks: ONE persistent kernel launch over the whole
+// pair list starts as soon as the small inputs are up; the pool follows in slices on the copy
+// stream, each slice followed by a 4-byte copy that raises a device-side counter of resident scans,
+// and the kernel waits (ld.acquire.sys) on that counter before it stages a pair.  No per-chunk
+// launch tails, copy and compute overlap down to the slice.
 // Results come back with one set of device-to-host copies at the end.  The call is synchronous.
 // Pinned host memory makes the copies asynchronous and faster; pageable memory works too.
 #include <cuda_runtime.h>
@@ -23,12 +28,15 @@ namespace {
 
 constexpr int kMaxChunks = 16;
 constexpr int kPipelineMinPairs = 2048;
+constexpr int kMaxSlices = 64;      // gated launch: pool slices announced to the running kernel
+constexpr int kMax2dPoints = 2048;  // the planar kernel's limit (api.cu)
 
 struct HostArena {
   char* base = nullptr;
   size_t cap = 0;
   cudaStream_t copy = nullptr, comp[2] = {nullptr, nullptr};
   cudaEvent_t ready[kMaxChunks] = {}, done[2] = {nullptr, nullptr}, small = nullptr;
+  unsigned int* progress_host = nullptr;   // pinned: cumulative scan counts, one per slice
   bool ok = false;
 };
 
@@ -45,6 +53,8 @@ bool arena_init(HostArena& a) {
   for (int k = 0; k < kMaxChunks; ++k)
     if (cudaEventCreateWithFlags(&a.ready[k], cudaEventDisableTiming) != cudaSuccess) return false;
   if (cudaEventCreateWithFlags(&a.small, cudaEventDisableTiming) != cudaSuccess) return false;
+  if (cudaHostAlloc(reinterpret_cast<void**>(&a.progress_host), kMaxSlices * sizeof(unsigned int),
+                    cudaHostAllocDefault) != cudaSuccess) return false;
   a.ok = true;
   return true;
 }
@@ -97,6 +107,83 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
   if (dim == 2)
     for (int b = 0; b < n_pairs; ++b)
       if (!keeps_plane(init + (size_t)b * 16)) { run_dim = 3; break; }
+
+  bool gated = run_dim == 2 && n_max <= kMax2dPoints && n_pairs >= kPipelineMinPairs;
+  if (const char* e = getenv("B200ICP_HOST_GATED")) gated = gated && atoi(e) != 0;   // 0: chunked path (A/B)
+  if (gated) {
+    Carver cv;
+    const size_t row_bytes = (size_t)n_max * 2 * sizeof(double);
+    const size_t o_scans = cv.take((size_t)n_scans * row_bytes);
+    const size_t o_counts = cv.take((size_t)n_scans * 4);
+    const size_t o_pairs = cv.take((size_t)n_pairs * 8);
+    const size_t o_init = cv.take((size_t)n_pairs * 128);
+    const size_t o_eps = cv.take((size_t)n_pairs * 8);
+    const size_t o_norm = cv.take((size_t)n_pairs);
+    const size_t o_T = cv.take((size_t)n_pairs * 128);
+    const size_t o_err = cv.take((size_t)n_pairs * 8);
+    const size_t o_iters = cv.take((size_t)n_pairs * 4);
+    const size_t o_status = cv.take((size_t)n_pairs * 4);
+    const size_t o_corr = corr_out ? cv.take((size_t)n_pairs * n_max * 4) : 0;
+    const size_t o_flag = cv.take(256);
+    size_t ws_bytes = 0;
+    const int rcw = b200icp_workspace_bytes(n_pairs, n_max, 2, &ws_bytes);
+    if (rcw != B200ICP_OK) return rcw;
+    const size_t o_ws = cv.take(ws_bytes);
+    if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
+    char* d = a.base;
+    B200_TRY(cudaMemsetAsync(d + o_flag, 0, 256, a.copy));
+    B200_TRY(cudaMemcpyAsync(d + o_counts, counts, (size_t)n_scans * 4, cudaMemcpyHostToDevice, a.copy));
+    B200_TRY(cudaMemcpyAsync(d + o_pairs, pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
+    B200_TRY(cudaMemcpyAsync(d + o_init, init, (size_t)n_pairs * 128, cudaMemcpyHostToDevice, a.copy));
+    B200_TRY(cudaMemcpyAsync(d + o_eps, epsilon, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
+    B200_TRY(cudaMemcpyAsync(d + o_norm, normalize, (size_t)n_pairs, cudaMemcpyHostToDevice, a.copy));
+    B200_TRY(cudaEventRecord(a.small, a.copy));
+    B200_TRY(cudaStreamWaitEvent(a.comp[0], a.small, 0));
+    const int rc_run = b200icp_run_gated(
+        reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts), n_scans, n_max,
+        2, reinterpret_cast<const int32_t*>(d + o_pairs), reinterpret_cast<const double*>(d + o_init),
+        reinterpret_cast<const double*>(d + o_eps), reinterpret_cast<const uint8_t*>(d + o_norm), n_pairs, max_iters,
+        stopping_thresh, reinterpret_cast<double*>(d + o_T), reinterpret_cast<double*>(d + o_err),
+        reinterpret_cast<int32_t*>(d + o_iters), reinterpret_cast<int32_t*>(d + o_status),
+        corr_out ? reinterpret_cast<int32_t*>(d + o_corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
+        reinterpret_cast<const unsigned int*>(d + o_flag));
+    // The pool follows in slices whether or not the launch succeeded (nothing waits on a failed one).
+    int n_slices = 24;
+    if (const char* e = getenv("B200ICP_HOST_SLICES")) { const int v = atoi(e); if (v >= 1) n_slices = v; }
+    if (n_slices > kMaxSlices) n_slices = kMaxSlices;
+    if (n_slices > n_scans) n_slices = n_scans;
+    int copied = 0;
+    bool copy_ok = true;
+    for (int c = 0; c < n_slices && copy_ok; ++c) {
+      const int upto = (int)((long long)n_scans * (c + 1) / n_slices);
+      if (upto > copied)
+        copy_ok = cudaMemcpyAsync(d + o_scans + (size_t)copied * row_bytes, scans + (size_t)copied * n_max * 2,
+                                  (size_t)(upto - copied) * row_bytes, cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
+      copied = upto;
+      a.progress_host[c] = (unsigned int)copied;
+      copy_ok = copy_ok && cudaMemcpyAsync(d + o_flag, a.progress_host + c, sizeof(unsigned int),
+                                           cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
+    }
+    if (!copy_ok) {   // release the waiting kernel, drain, report
+      cudaGetLastError();
+      cudaMemset(d + o_flag, 0xff, sizeof(unsigned int));
+      cudaStreamSynchronize(a.comp[0]);
+      cudaStreamSynchronize(a.copy);
+      cudaGetLastError();
+      return B200ICP_ERR_CUDA;
+    }
+    B200_TRY(cudaEventRecord(a.done[0], a.comp[0]));
+    B200_TRY(cudaStreamWaitEvent(a.copy, a.done[0], 0));
+    if (rc_run == B200ICP_OK) {
+      B200_TRY(cudaMemcpyAsync(T_out, d + o_T, (size_t)n_pairs * 128, cudaMemcpyDeviceToHost, a.copy));
+      if (err_out) B200_TRY(cudaMemcpyAsync(err_out, d + o_err, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, a.copy));
+      if (iters_out) B200_TRY(cudaMemcpyAsync(iters_out, d + o_iters, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
+      if (status_out) B200_TRY(cudaMemcpyAsync(status_out, d + o_status, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
+      if (corr_out) B200_TRY(cudaMemcpyAsync(corr_out, d + o_corr, (size_t)n_pairs * n_max * 4, cudaMemcpyDeviceToHost, a.copy));
+    }
+    B200_TRY(cudaStreamSynchronize(a.copy));
+    return rc_run;
+  }
 
   // chunks of the pair list and the pool prefix each one needs
   int n_chunks = 1;

@@ -321,6 +321,13 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 
     // ---- stage both scans with TMA bulk copies --------------------------------
     if (tid == 0) {
+      if (p.ready_scans) {   // gated launch: wait until the copy stream has delivered both scans
+        const unsigned need = (unsigned)max(si, ti) + 1u;
+        // bounded: a caller whose copies failed must not hang the device (it raises the counter to
+        // 0xffffffff on failure; this cap is the last resort, several seconds)
+        for (unsigned spins = 0; ld_acquire_sys(p.ready_scans) < need && spins < (1u << 25); ++spins) __nanosleep(200);
+        fence_proxy_async_global();
+      }
       fence_proxy_async();
       mbar_expect_tx(mbar, (uint32_t)(ns + nt) * 16u);
       tma_load_1d(s64, p.scans + (size_t)si * p.n_max * 2, (uint32_t)ns * 16u, mbar);

@@ -167,6 +167,13 @@ __device__ __forceinline__ void fence_proxy_async_global() {
 __device__ __forceinline__ void fence_mbar_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
+// system-scope acquire load: pairs with a flag written by a host-to-device copy that follows the
+// data it announces in stream order
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned int* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 // bytes must be a multiple of 16; both addresses 16-byte aligned.
 __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes,
                                             uint64_t* bar) {
@@ -226,6 +233,9 @@ struct RunParams {
   double* peer_out[kMaxPeers];
   int n_peers;
   long long peer_row0;
+  // gated launch (b200icp_run_gated): scans [0, *ready_scans) of the pool are resident; the value
+  // is raised by copies on another stream while the kernel runs.  Null: the whole pool is resident.
+  const unsigned int* ready_scans;
 };
 
 // kept out of line: atan2's slow path must not widen the register footprint of the ICP loops
