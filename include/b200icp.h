@@ -103,14 +103,16 @@ int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_m
  * ready_scans points to a device uint32 holding the number of leading pool rows that are resident;
  * the caller raises it from another stream (e.g. a 4-byte copy after each slice of the pool) while
  * the kernel runs, and the kernel waits on it (system-scope acquire) before it stages a pair.
- * Everything else (counts, pairs, init, epsilon, normalize) must be resident at launch.  This is
+ * Everything else (counts, pairs, init, epsilon, normalize) must be resident at launch.
+ * peer_pose_out / n_peers / peer_row0 as in b200icp_run_exchange (NULL, 0, 0: no exchange).  This is
  * how b200icp_run_host overlaps the upload of the pool with ONE launch over the whole pair list. */
 int b200icp_run_gated(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
                       const int32_t* pairs, const double* init, const double* epsilon,
                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                       int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
-                      const unsigned int* ready_scans);
+                      const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
+                      long long peer_row0);
 
 /* b200icp_run with the multi-GPU pose exchange fused into the kernel epilogue: the thread that
  * finishes pair b also stores its packed row (x, y, theta, error) -- the b200icp_pack_poses

@@ -27,7 +27,8 @@ SIGNATURES = {
                                      ctypes.c_longlong]),
     "b200icp_run_gated": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
-                                  c_void_p, c_void_p, c_size_t, c_void_p, c_void_p]),
+                                  c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_int,
+                                  ctypes.c_longlong]),
     "b200icp_run_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),

@@ -239,11 +239,12 @@ int b200icp_run_gated(const double* scans, const int32_t* counts, int n_scans, i
                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                       int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
-                      const unsigned int* ready_scans) {
+                      const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
+                      long long peer_row0) {
   if (!ready_scans) return B200ICP_ERR_BAD_ARG;
   return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
                     stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
-                    workspace_bytes, stream, nullptr, 0, 0, ready_scans);
+                    workspace_bytes, stream, peer_pose_out, n_peers, peer_row0, ready_scans);
 }
 
 int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,

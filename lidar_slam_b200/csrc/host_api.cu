@@ -9,10 +9,11 @@
 // to the device in slices while the pair list runs in chunks: before chunk c starts, the prefix
 // of the pool its pairs reference is resident (consecutive pairs (i, i-1) need the pool in
 // order, so copy and compute overlap; arbitrary pair lists simply wait for more of the pool).
-// Planar batches take the GATED path instead of chunks: ONE persistent kernel launch over the whole
-// pair list starts as soon as the small inputs are up; the pool follows in slices on the copy
-// stream, each slice followed by a 4-byte copy that raises a device-side counter of resident scans,
-// and the kernel waits (ld.acquire.sys) on that counter before it stages a pair.  No per-chunk
+// Planar batches take the GATED path instead of chunks: the pool is enqueued in slices on the copy
+// stream, each slice followed by a 4-byte copy that raises a device-side counter of resident scans;
+// ONE persistent kernel launch over the whole pair list is issued right behind them on a compute
+// stream (it only depends on the small inputs) and waits (ld.acquire.sys) on that counter before it
+// stages a pair.  No per-chunk
 // launch tails, copy and compute overlap down to the slice.
 // Results come back with one set of device-to-host copies at the end.  The call is synchronous.
 // Pinned host memory makes the copies asynchronous and faster; pageable memory works too.
@@ -139,18 +140,11 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
     B200_TRY(cudaMemcpyAsync(d + o_norm, normalize, (size_t)n_pairs, cudaMemcpyHostToDevice, a.copy));
     B200_TRY(cudaEventRecord(a.small, a.copy));
     B200_TRY(cudaStreamWaitEvent(a.comp[0], a.small, 0));
-    const int rc_run = b200icp_run_gated(
-        reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts), n_scans, n_max,
-        2, reinterpret_cast<const int32_t*>(d + o_pairs), reinterpret_cast<const double*>(d + o_init),
-        reinterpret_cast<const double*>(d + o_eps), reinterpret_cast<const uint8_t*>(d + o_norm), n_pairs, max_iters,
-        stopping_thresh, reinterpret_cast<double*>(d + o_T), reinterpret_cast<double*>(d + o_err),
-        reinterpret_cast<int32_t*>(d + o_iters), reinterpret_cast<int32_t*>(d + o_status),
-        corr_out ? reinterpret_cast<int32_t*>(d + o_corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
-        reinterpret_cast<const unsigned int*>(d + o_flag));
-    // The pool follows in slices whether or not the launch succeeded (nothing waits on a failed one).
+    // The slices are ENQUEUED before the launch: if something serialises launches (a profiler,
+    // CUDA_LAUNCH_BLOCKING) the kernel must never wait for a copy the host has not issued yet.
     int n_slices = 24;
     if (const char* e = getenv("B200ICP_HOST_SLICES")) { const int v = atoi(e); if (v >= 1) n_slices = v; }
-    if (n_slices > kMaxSlices) n_slices = kMaxSlices;
+    if (n_slices > kMaxSlices - 1) n_slices = kMaxSlices - 1;   // the last pinned word receives the gave-up flag
     if (n_slices > n_scans) n_slices = n_scans;
     int copied = 0;
     bool copy_ok = true;
@@ -164,14 +158,20 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
       copy_ok = copy_ok && cudaMemcpyAsync(d + o_flag, a.progress_host + c, sizeof(unsigned int),
                                            cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
     }
-    if (!copy_ok) {   // release the waiting kernel, drain, report
+    if (!copy_ok) {
       cudaGetLastError();
-      cudaMemset(d + o_flag, 0xff, sizeof(unsigned int));
-      cudaStreamSynchronize(a.comp[0]);
       cudaStreamSynchronize(a.copy);
       cudaGetLastError();
       return B200ICP_ERR_CUDA;
     }
+    const int rc_run = b200icp_run_gated(
+        reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts), n_scans, n_max,
+        2, reinterpret_cast<const int32_t*>(d + o_pairs), reinterpret_cast<const double*>(d + o_init),
+        reinterpret_cast<const double*>(d + o_eps), reinterpret_cast<const uint8_t*>(d + o_norm), n_pairs, max_iters,
+        stopping_thresh, reinterpret_cast<double*>(d + o_T), reinterpret_cast<double*>(d + o_err),
+        reinterpret_cast<int32_t*>(d + o_iters), reinterpret_cast<int32_t*>(d + o_status),
+        corr_out ? reinterpret_cast<int32_t*>(d + o_corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
+        reinterpret_cast<const unsigned int*>(d + o_flag), nullptr, 0, 0);
     B200_TRY(cudaEventRecord(a.done[0], a.comp[0]));
     B200_TRY(cudaStreamWaitEvent(a.copy, a.done[0], 0));
     if (rc_run == B200ICP_OK) {
@@ -180,8 +180,12 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
       if (iters_out) B200_TRY(cudaMemcpyAsync(iters_out, d + o_iters, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
       if (status_out) B200_TRY(cudaMemcpyAsync(status_out, d + o_status, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
       if (corr_out) B200_TRY(cudaMemcpyAsync(corr_out, d + o_corr, (size_t)n_pairs * n_max * 4, cudaMemcpyDeviceToHost, a.copy));
+      // workspace word 5: the kernel gave up waiting for the pool (never expected; results void)
+      B200_TRY(cudaMemcpyAsync(a.progress_host + kMaxSlices - 1, d + o_ws + 20, sizeof(unsigned int),
+                               cudaMemcpyDeviceToHost, a.copy));
     }
     B200_TRY(cudaStreamSynchronize(a.copy));
+    if (rc_run == B200ICP_OK && a.progress_host[kMaxSlices - 1] != 0u) return B200ICP_ERR_CUDA;
     return rc_run;
   }
 

@@ -323,9 +323,19 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     if (tid == 0) {
       if (p.ready_scans) {   // gated launch: wait until the copy stream has delivered both scans
         const unsigned need = (unsigned)max(si, ti) + 1u;
-        // bounded: a caller whose copies failed must not hang the device (it raises the counter to
-        // 0xffffffff on failure; this cap is the last resort, several seconds)
-        for (unsigned spins = 0; ld_acquire_sys(p.ready_scans) < need && spins < (1u << 25); ++spins) __nanosleep(200);
+        // Bounded (last resort): a caller whose copies never arrive must not hang the device.  A
+        // wait of more than 5 s gives up, and from then on nobody waits; queue[5] tells the host
+        // side that the results are void.
+        if (ld_acquire_sys(p.ready_scans) < need) {
+          volatile unsigned* gave_up = p.queue + 5;
+          unsigned long long t0, t1;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+          while (ld_acquire_sys(p.ready_scans) < need && *gave_up == 0u) {
+            __nanosleep(500);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 5000000000ull) *gave_up = 1u;
+          }
+        }
         fence_proxy_async_global();
       }
       fence_proxy_async();

@@ -111,6 +111,39 @@ def _side_streams(dev):
     return _SIDE_STREAMS[key]
 
 
+_GATE_SLICES = 24
+_GATE_VALUES = {}
+
+
+def _copy_pool_gated(host_pool, dev_pool, dev, launch_gated):
+    """Host -> device copy of the scan pool under ONE launch (b200icp_run_gated): the pool goes up in
+    slices on the copy stream, each followed by a 4-byte copy that raises a device counter of resident
+    scans; the kernel, launched right behind on the current stream, waits on that counter per pair."""
+    cur = torch.cuda.current_stream(dev)
+    copy_s = _side_streams(dev)[0]
+    n_scans = host_pool.shape[0]
+    k = max(1, min(_GATE_SLICES, n_scans))
+    key = (n_scans, k)
+    if key not in _GATE_VALUES:
+        _GATE_VALUES[key] = torch.tensor([n_scans * (c + 1) // k for c in range(k)], dtype=torch.int32).pin_memory()
+    vals = _GATE_VALUES[key]
+    flag = torch.zeros((64,), dtype=torch.int32, device=dev)
+    flag.record_stream(copy_s)
+    copy_s.wait_stream(cur)            # counter zeroed, small inputs uploaded
+    # copies are enqueued BEFORE the launch: a tool that serialises launches (profiler,
+    # CUDA_LAUNCH_BLOCKING) must never leave the kernel waiting for a copy not yet issued
+    with torch.cuda.stream(copy_s):
+        lo = 0
+        for c in range(k):
+            hi = int(vals[c])
+            if hi > lo:
+                dev_pool[lo:hi].copy_(host_pool[lo:hi], non_blocking=True)
+            flag[:1].copy_(vals[c:c + 1], non_blocking=True)
+            lo = hi
+    launch_gated(flag)
+    cur.wait_stream(copy_s)
+
+
 def _copy_pool_pipelined(host_pool, dev_pool, pairs_host, dev, launch_chunk):
     """Host -> device copy of the scan pool overlapped with the alignment: the pair list is cut
     into chunks; before chunk c runs, the prefix of the pool it references (rows up to its
@@ -239,6 +272,20 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
                 _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
                 _stream_ptr()), "b200icp_run")
 
+    if host_pool is not None and dim == 2 and n_max <= 2048 and (planar_ok or not planar_fallback):
+        def launch_gated(flag):
+            peers, n_peers = None, 0
+            if peer_pose_ptrs:
+                peers_arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
+                peers, n_peers = ctypes.cast(peers_arr, ctypes.c_void_p), len(peer_pose_ptrs)
+            with torch.cuda.device(dev):
+                _lib.check(lib.b200icp_run_gated(
+                    _ptr(scans), _ptr(counts), n_scans, n_max, dim, _ptr(pairs), _ptr(init), _ptr(eps), _ptr(norm),
+                    n_pairs, int(max_iters), float(stopping_thresh), _ptr(T), _ptr(err), _ptr(iters), _ptr(status),
+                    _ptr(corr), _ptr(ws), ws.numel(), _stream_ptr(), _ptr(flag), peers, n_peers, int(peer_row0)),
+                    "b200icp_run_gated")
+        _copy_pool_gated(host_pool, scans, dev, launch_gated)
+        return IcpBatchResult(T, err, iters, status, corr)
     if host_pool is not None:
         _copy_pool_pipelined(host_pool, scans, pairs_host, dev,
                              None if (dim == 2 and planar_fallback and not planar_ok) else
