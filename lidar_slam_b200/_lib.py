@@ -63,6 +63,9 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
+    global LIB_PATH
+    if os.environ.get("B200ICP_LIB"):          # developer A/B: another build of the same library
+        LIB_PATH = os.environ["B200ICP_LIB"]
     if not os.path.exists(LIB_PATH):
         raise RuntimeError(
             f"{LIB_PATH} is missing: build it with `python -m lidar_slam_b200.build` "

@@ -122,7 +122,10 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (p.n_max <= 256) return launch2d<2, 4, 8>(p, stream, d.sms);
     if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
     if (p.n_max <= 1280) {
-      return launch2d<5, 8, 3>(p, stream, d.sms);
+      // pruned kernel: 64 registers, 4 CTAs/SM (it is latency-bound: +5 % over 3 CTAs, measured);
+      // exhaustive kernel: 80 registers, 3 CTAs/SM (FMA-bound, spills would sit in the sweep)
+      return prune_enabled() ? launch2d_variant<5, 8, 4, true>(p, stream, d.sms)
+                             : launch2d_variant<5, 8, 3, false>(p, stream, d.sms);
     }
     return launch2d<8, 8, 2>(p, stream, d.sms);
   }

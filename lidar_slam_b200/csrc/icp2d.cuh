@@ -59,7 +59,7 @@ __host__ __device__ inline Smem2dLayout smem2d_layout(int n_max, int warps, bool
   L.off_red = o; o += (size_t)2 * warps * kRed2d * 8;
   L.off_part = o; o += prune ? 0 : (size_t)(warps - 1) * warps * 32 * 8;   // shared rows: (best, second) per warp and lane
   L.off_bb = o; o += prune ? (size_t)64 * 16 : 0;                           // target-block boxes (xmin, xmax, ymin, ymax)
-  L.off_rb = o; o += prune ? (size_t)warps * rows_per_thread * 16 : 0;      // source-row boxes, per warp and row slot
+  L.off_rb = o; o += prune ? (size_t)warps * 128 : 0;                       // per-warp scratch: bbox of the matched pairs
   L.off_ctl = o; o += 64;
   L.total = o;
   return L;
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
   double* red = reinterpret_cast<double*>(smem_raw + L.off_red);
   uint2* part = reinterpret_cast<uint2*>(smem_raw + L.off_part);
   float4* bb = reinterpret_cast<float4*>(smem_raw + L.off_bb);
-  float4* rb = reinterpret_cast<float4*>(smem_raw + L.off_rb) + (threadIdx.x >> 5) * R;
+  double* wscr = reinterpret_cast<double*>(smem_raw + L.off_rb) + (threadIdx.x >> 5) * 16;
   uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw + L.off_ctl);
   int* s_pair = reinterpret_cast<int*>(smem_raw + L.off_ctl + 16);
 
@@ -386,6 +386,15 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     tmax = tmax * (1.0f + 4.0f * kU);   // fp32 rounding of the inputs
     ox /= (double)nt; oy /= (double)nt;  // shift origin for the one-pass covariance
     __syncthreads();                     // red[] is reused by the passes below
+    if constexpr (PRUNE) {
+      // The pose and the origin are warp-uniform: the pruned kernel keeps them in its per-warp
+      // scratch (read back where needed) instead of 16 registers per thread across the row loop.
+      if (lane == 0) {
+        wscr[8] = r00; wscr[9] = r01; wscr[10] = r10; wscr[11] = r11; wscr[12] = tx; wscr[13] = ty;
+        wscr[14] = ox; wscr[15] = oy;
+      }
+      __syncwarp();
+    }
 
     PHASE(0);
     const double epsilon = p.nearest_only ? 0.0 : p.epsilon[pair];
@@ -419,6 +428,10 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
       float qx[R], qy[R];
       unsigned best[R], second[R];
       if constexpr (PRUNE) {
+        // bounding box of the matched pairs (normalised error only): kept per warp in shared
+        // memory instead of 16 registers per thread (minima and maxima are order-independent)
+        if (normalize && lane < 8) wscr[lane] = (lane & 1) ? -kInf : kInf;
+        __syncwarp();
         // One rolled loop over this warp's rows: transform, pruned fp32 sweep, exact resolution,
         // sums.  (A rolled loop keeps the kernel small: the exhaustive variant's five-row unrolled
         // phases no longer pay once the sweep is pruned -- instruction fetch was the top stall.)
@@ -428,9 +441,10 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           const bool v = j < ns;
           double qdx = 0.0, qdy = 0.0;
           if (v) {
+            const volatile double* ws = wscr;
             const double2 s = s64[j];
-            qdx = fma(r00, s.x, fma(r01, s.y, tx));
-            qdy = fma(r10, s.x, fma(r11, s.y, ty));
+            qdx = fma(ws[8], s.x, fma(ws[9], s.y, ws[12]));
+            qdy = fma(ws[10], s.x, fma(ws[11], s.y, ws[13]));
           }
           const float fqx = (float)qdx, fqy = (float)qdy;
           unsigned bst, snd;
@@ -501,25 +515,40 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           // 4. float64 sums over the matched pairs
           if (v) {
             const double2 t = t64[c];
-            const double ux = qdx - ox, uy = qdy - oy, vx = t.x - ox, vy = t.y - oy;
+            const double wox = static_cast<const volatile double*>(wscr)[14];
+            const double woy = static_cast<const volatile double*>(wscr)[15];
+            const double ux = qdx - wox, uy = qdy - woy, vx = t.x - wox, vy = t.y - woy;
             acc[0] += ux; acc[1] += uy; acc[2] += vx; acc[3] += vy;
             acc[4] = fma(ux, vx, acc[4]); acc[5] = fma(ux, vy, acc[5]);
             acc[6] = fma(uy, vx, acc[6]); acc[7] = fma(uy, vy, acc[7]);
             const double ex = qdx - t.x, ey = qdy - t.y;
             acc[8] += ex * ex + ey * ey;
-            if (normalize) {
-              acc[9] = fmin(acc[9], qdx);   acc[10] = fmax(acc[10], qdx);
-              acc[11] = fmin(acc[11], qdy); acc[12] = fmax(acc[12], qdy);
-              acc[13] = fmin(acc[13], t.x); acc[14] = fmax(acc[14], t.x);
-              acc[15] = fmin(acc[15], t.y); acc[16] = fmax(acc[16], t.y);
-            }
             if (p.nearest_only && p.dist2_out)
               p.dist2_out[(size_t)pair * p.n_max + j] = ex * ex + ey * ey;
+          }
+          if (normalize) {   // warp-uniform
+            double2 t = make_double2(0.0, 0.0);
+            if (v) t = t64[c];
+            const double m0 = warp_min(v ? qdx : kInf), m1 = warp_max(v ? qdx : -kInf);
+            const double m2 = warp_min(v ? qdy : kInf), m3 = warp_max(v ? qdy : -kInf);
+            const double m4 = warp_min(v ? t.x : kInf), m5 = warp_max(v ? t.x : -kInf);
+            const double m6 = warp_min(v ? t.y : kInf), m7 = warp_max(v ? t.y : -kInf);
+            if (lane == 0) {
+              wscr[0] = fmin(wscr[0], m0); wscr[1] = fmax(wscr[1], m1);
+              wscr[2] = fmin(wscr[2], m2); wscr[3] = fmax(wscr[3], m3);
+              wscr[4] = fmin(wscr[4], m4); wscr[5] = fmax(wscr[5], m5);
+              wscr[6] = fmin(wscr[6], m6); wscr[7] = fmax(wscr[7], m7);
+            }
           }
           // the row's match enters the register queue at the top: after the loop row r sits in slot R - nr + r
 #pragma unroll
           for (int i = 0; i + 1 < R; ++i) corr[i] = corr[i + 1];
           corr[R - 1] = c;
+        }
+        if (normalize) {
+          __syncwarp();
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[kSums2d + k] = wscr[k];
         }
         PHASE(1);
       } else {
@@ -697,7 +726,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         }  // !PRUNE
 #pragma unroll
         for (int k = 0; k < kSums2d; ++k) acc[k] = warp_sum(acc[k]);
-        if (normalize) {
+        if (!PRUNE && normalize) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             acc[kSums2d + 2 * k] = warp_min(acc[kSums2d + 2 * k]);
@@ -766,6 +795,11 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           const double co = den / h, sn = num / h;
           d00 = co; d01 = sn; d10 = sn; d11 = -co; dz = -1.0;
         }
+        if constexpr (PRUNE) {
+          const volatile double* ws = wscr;
+          r00 = ws[8]; r01 = ws[9]; r10 = ws[10]; r11 = ws[11]; tx = ws[12]; ty = ws[13];
+          ox = ws[14]; oy = ws[15];
+        }
         const double qbx = ox + mqx, qby = oy + mqy, pbx = ox + mpx, pby = oy + mpy;
         const double dtx = pbx - (d00 * qbx + d01 * qby);
         const double dty = pby - (d10 * qbx + d11 * qby);
@@ -773,6 +807,13 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
         const double n10 = d10 * r00 + d11 * r10, n11 = d10 * r01 + d11 * r11;
         const double ntx = d00 * tx + d01 * ty + dtx, nty = d10 * tx + d11 * ty + dty;
         r00 = n00; r01 = n01; r10 = n10; r11 = n11; tx = ntx; ty = nty; zs *= dz;
+        if constexpr (PRUNE) {
+          __syncwarp();            // every lane has read the old pose
+          if (lane == 0) {
+            wscr[8] = r00; wscr[9] = r01; wscr[10] = r10; wscr[11] = r11; wscr[12] = tx; wscr[13] = ty;
+          }
+          __syncwarp();
+        }
         status = stop_test(st, err, epsilon, p.max_iters, p.stopping_thresh);
       }
       PHASE(6);
