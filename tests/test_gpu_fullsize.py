@@ -87,8 +87,9 @@ def test_config5_shard_generated_on_device():
 
 
 def test_pipelined_host_inputs_equal_resident_inputs():
-    """Pinned host buffers take the streamed path (pool copied in slices on a copy stream while
-    earlier pair chunks run on two compute streams): bit-identical to device-resident inputs."""
+    """Pinned host buffers take the streamed path (pool copied in slices on a copy stream under one
+    gated launch that waits per pair for its scans): bit-identical to device-resident inputs, for a
+    sorted pair list and for a reversed one (whose first pairs need the end of the pool)."""
     import lidar_slam_b200 as eng
     from lidar_slam_b200 import synth
     b = synth.odometry_batch(4955, seed=21, device="cuda")

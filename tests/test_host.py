@@ -216,6 +216,15 @@ def test_c_abi_argument_validation_without_a_device():
     assert lib.b200icp_run(one, one, 1, 2, 2, one, one, one, one, 1, -1, 1e-4, one, one, one, one, null, one, 256, null) == -1
     assert lib.b200icp_run_exchange(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
                                     null, null, 3, 0) == -1                      # peers announced but no array
+    # gated entry: the counter of resident scans is mandatory, and only the planar kernel waits on one
+    assert lib.b200icp_run_gated(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
+                                 null, null, null, 0, 0) == -1                   # no ready_scans
+    assert lib.b200icp_run_gated(one, one, 1, 2, 3, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
+                                 null, one, null, 0, 0) == -1                    # 3-D: general kernel
+    assert lib.b200icp_run_gated(one, one, 1, 4096, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one,
+                                 256, null, one, null, 0, 0) == -1               # planar but n_max > 2048
+    assert lib.b200icp_run_gated(one, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null, one, 256,
+                                 null, one, null, 2, 0) == -1                    # peers announced but no array
     # host-buffer entry: bad arguments, the empty pair list (nothing to do), and no device here
     assert lib.b200icp_run_host(null, one, 1, 2, 2, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null) == -1
     assert lib.b200icp_run_host(one, one, 1, 3, 3, one, one, one, one, 1, 5, 1e-4, one, one, one, one, null) == -1  # odd row
