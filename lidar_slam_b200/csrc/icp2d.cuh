@@ -9,11 +9,14 @@
 //           and target scans into shared memory; the target is also kept as
 //           fp32 (x,y) pairs for the search.                      [icp.py:153-161]
 //   pass k  1. q = T_k s in float64, rounded to fp32 for the search [icp.py:116]
-//           2. exhaustive fp32 nearest-neighbour sweep: every thread keeps R
-//              source points in registers, targets are broadcast from shared
-//              memory as LDS.128 (two targets), block minima tracked with
-//              FMNMX3; per 32-target block the best and second-best (value |
-//              block id) are kept.                                  [icp.py:117]
+//           2. fp32 nearest-neighbour sweep over 32-target blocks, targets broadcast
+//              from shared memory as LDS.128 (two targets), packed fp32x2 math,
+//              FMNMX3 minima; per row of 32 queries the best and second-best
+//              (value | block id) are kept.  Default (PRUNE): one row at a time,
+//              blocks whose bounding-box lower bound exceeds the candidate
+//              threshold are skipped -- exact, see sweep_row_pruned.  PRUNE=false
+//              (B200ICP_SWEEP=exhaustive): every block, R rows per thread in
+//              registers.                                           [icp.py:117]
 //           3. exactness: the best block is rescanned, every candidate within a
 //              proven slack of the fp32 minimum is re-evaluated in float64 from
 //              the original coordinates; if a second block is within the slack
