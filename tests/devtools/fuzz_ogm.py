@@ -1,7 +1,7 @@
 """Randomised bit-exactness run of the occupancy grid against the oracle (developer tool, GPU box).
-python tools/fuzz_ogm.py [seconds] [seed]"""
+python tests/devtools/fuzz_ogm.py [seconds] [seed]"""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from lidar_slam_b200 import ogm
 from oracle import ogm_oracle as oo

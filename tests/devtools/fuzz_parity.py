@@ -1,7 +1,7 @@
 """Randomised parity run (developer tool, GPU box): random sizes / dimensions / motions / stop
-parameters, device result against the oracle.  python tools/fuzz_parity.py [seconds] [seed]"""
+parameters, device result against the oracle.  python tests/devtools/fuzz_parity.py [seconds] [seed]"""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import lidar_slam_b200 as eng
 from lidar_slam_b200 import hostapi

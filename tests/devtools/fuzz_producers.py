@@ -1,7 +1,7 @@
 """Randomised bit-exactness run of scan construction, the range filter and the texture splat against
-their oracles (developer tool, GPU box).  python tools/fuzz_producers.py [seconds] [seed]"""
+their oracles (developer tool, GPU box).  python tests/devtools/fuzz_producers.py [seconds] [seed]"""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from lidar_slam_b200 import scans, texture_mapping as tm
 from oracle import scan_oracle as so, texture_oracle as to

@@ -1,7 +1,7 @@
 """Small, fixed workloads for ncu captures of the non-headline kernels (one case per run):
-   python tools/profile_cases.py ogm|texture|icp3d|scans"""
+   python tests/devtools/profile_cases.py ogm|texture|icp3d|scans"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import lidar_slam_b200 as eng
 from lidar_slam_b200 import synth, ogm, scans, texture_mapping as tm

@@ -1,6 +1,6 @@
-"""Tiny run of every kernel for compute-sanitizer (memcheck):  compute-sanitizer --tool memcheck python tools/sanitize_cases.py"""
+"""Tiny run of every kernel for compute-sanitizer (memcheck):  compute-sanitizer --tool memcheck python tests/devtools/sanitize_cases.py"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import lidar_slam_b200 as eng
 from lidar_slam_b200 import synth, ogm, scans, texture_mapping as tm, engine

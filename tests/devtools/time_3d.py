@@ -1,7 +1,7 @@
 """Developer timing probe (not the benchmark): configs 1 / 4 -- the 24-yaw initialisation sweep of
 code/icp_warm_up/test_icp.py on synthetic 3-D objects, all (target, yaw) problems in one launch."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import lidar_slam_b200 as eng
 from lidar_slam_b200 import synth, engine

@@ -2,7 +2,7 @@
 path at config-2 size -- scan construction, occupancy-grid mapping, texture mapping -- with the
 CPU oracle timed on a bounded sample beside each."""
 import json, os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from lidar_slam_b200 import synth, scans, ogm, texture_mapping as tm
 from oracle import scan_oracle as so, ogm_oracle as oo, texture_oracle as to

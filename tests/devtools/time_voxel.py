@@ -1,6 +1,6 @@
 """Developer timing of voxel_downsample on the device against the oracle (row F2)."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from lidar_slam_b200 import engine, synth
 from oracle import icp_oracle as orc

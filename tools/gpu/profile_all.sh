@@ -6,8 +6,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-fi
     python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/p_ncu_bench.log 2>&1
 for c in ogm texture icp3d scans; do
   case $c in ogm) k=ogm_apply;; texture) k=texture_paint;; icp3d) k=icp3d;; scans) k=ranges_to_scans;; esac
-  python tools/profile_cases.py $c > gpurun_out/p_plain_$c.log 2>&1 &&
+  python tests/devtools/profile_cases.py $c > gpurun_out/p_plain_$c.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -o gpurun_out/p_$c \
-      python tools/profile_cases.py $c > gpurun_out/p_ncu_$c.log 2>&1
+      python tests/devtools/profile_cases.py $c > gpurun_out/p_ncu_$c.log 2>&1
 done
 ls -la gpurun_out | head -40
