@@ -120,6 +120,111 @@ def test_box_lower_bound_never_exceeds_the_fp32_candidate_distance():
             assert lb <= d.min(), (scale, spread, float(lb), float(d.min()))
 
 
+def _candidate_threshold(trunc_min, a_bound):
+    """float32 restatement of candidate_threshold() in csrc/icp_common.cuh (trunc_rel = 2^-16)."""
+    f32 = np.float32
+    hi = (trunc_min.astype(np.float64) * 2.0 ** -16 + trunc_min.astype(np.float64)).astype(f32)
+    thr = (hi + f32(4) * _slack(hi, a_bound)).astype(f32)
+    return (thr.astype(np.float64) * (4 * 2.0 ** -24) + thr.astype(np.float64)).astype(f32)
+
+
+def _trunc(d):
+    return (d.view(np.uint32) & np.uint32(0xffffffc0)).view(np.float32)
+
+
+@pytest.mark.parametrize("kind", ["lidar", "lidar_shifted", "clusters", "shuffled", "two_blocks"])
+def test_pruned_search_emulation_equals_float64_exhaustive_search(kind):
+    """numpy restatement of the pruned NN search of csrc/icp2d.cuh (sweep_row_pruned + resolution), in
+    float32 where the kernel is float32: boxes, lower bounds, two seed blocks, the threshold of the
+    current best, the blocks that survive it, then candidates <= thr of the best block re-evaluated in
+    float64 (all targets if a second swept block is within thr).  The result must be the float64
+    exhaustive argmin (lowest index on ties) for every query -- the property the GPU tests check
+    against the device; this test checks the ALGORITHM on the CPU, and that blocks are really skipped."""
+    f32 = np.float32
+    rng = np.random.default_rng({"lidar": 1, "lidar_shifted": 2, "clusters": 3, "shuffled": 4, "two_blocks": 5}[kind])
+    if kind in ("lidar", "lidar_shifted", "shuffled"):
+        from lidar_slam_b200 import synth
+        b = synth.odometry_batch(2, seed=31)
+        c = b["counts"].numpy()
+        tgt, src = b["scans"][0, :c[0]].numpy().copy(), b["scans"][1, :c[1]].numpy().copy()
+        if kind == "lidar_shifted":
+            tgt += np.array([310.5, -127.25]); src += np.array([310.5, -127.25])
+        if kind == "shuffled":
+            tgt = tgt[rng.permutation(len(tgt))]
+    elif kind == "clusters":
+        centres = rng.uniform(-20, 20, size=(9, 2))
+        tgt = np.concatenate([cc + rng.normal(scale=0.05, size=(40, 2)) for cc in centres])
+        tgt[31] = tgt[32]
+        src = tgt[rng.permutation(len(tgt))[:200]] + rng.normal(scale=0.003, size=(200, 2))
+        src[0] = tgt[31]
+    else:
+        tgt = rng.uniform(-1, 1, size=(50, 2))
+        src = rng.uniform(-1, 1, size=(70, 2))
+    nt, ns = len(tgt), len(src)
+    nblk = (nt + 31) // 32
+    t32, q32 = tgt.astype(f32), src.astype(f32)
+    tmax = f32(np.abs(t32).max()) * (f32(1) + f32(4 * 2.0 ** -24))
+
+    def fma32(a, b_, c_):
+        return (a.astype(np.float64) * b_.astype(np.float64) + c_.astype(np.float64)).astype(f32)
+
+    def d32(q, t):          # [nq, ntargets]
+        dx = (q[:, None, 0] - t[None, :, 0]).astype(f32)
+        dy = (q[:, None, 1] - t[None, :, 1]).astype(f32)
+        return fma32(dx, dx, (dy * dy).astype(f32))
+
+    boxes = np.array([[t32[k * 32:(k + 1) * 32, 0].min(), t32[k * 32:(k + 1) * 32, 0].max(),
+                       t32[k * 32:(k + 1) * 32, 1].min(), t32[k * 32:(k + 1) * 32, 1].max()] for k in range(nblk)], f32)
+    d64_all = ((src[:, None, :] - tgt[None, :, :]) ** 2).sum(-1)
+    want = d64_all.argmin(1)                       # numpy argmin: lowest index on ties
+    swept_total = 0
+    for r0 in range(0, ns, 32):
+        q = q32[r0:r0 + 32]
+        qb = (q[:, 0].min(), q[:, 0].max(), q[:, 1].min(), q[:, 1].max())
+        ex = np.maximum(np.maximum(boxes[:, 0] - qb[1], qb[0] - boxes[:, 1]), f32(0)).astype(f32)
+        ey = np.maximum(np.maximum(boxes[:, 2] - qb[3], qb[2] - boxes[:, 3]), f32(0)).astype(f32)
+        lb = fma32(ex, ex, (ey * ey).astype(f32))
+        key = (lb.view(np.uint32) & np.uint32(0xffffffc0)) | np.arange(nblk, dtype=np.uint32)
+        seeds = list(np.argsort(key)[:2])
+        blockmin = {}
+
+        def sweep(k):
+            blockmin[k] = d32(q, t32[k * 32:(k + 1) * 32]).min(1)
+        for k in seeds:
+            sweep(k)
+
+        def best_second():
+            ks = sorted(blockmin)
+            pk = np.stack([_trunc(blockmin[k]).view(np.uint32) | np.uint32(k) for k in ks], 1)
+            order = np.sort(pk, 1)
+            return order[:, 0], (order[:, 1] if len(ks) > 1 else np.full(len(q), 0xffffffff, np.uint32))
+        best, _ = best_second()
+        a_bound = np.maximum(np.abs(q[:, 0]), np.abs(q[:, 1])) * (f32(1) + f32(4 * 2.0 ** -24)) + tmax
+        thr = _candidate_threshold((best & np.uint32(0xffffffc0)).view(f32), a_bound)
+        bound = thr.view(np.uint32).max()
+        for k in range(nblk):
+            if k not in blockmin and not (lb[k:k + 1].view(np.uint32)[0] > bound):
+                sweep(k)
+        swept_total += len(blockmin)
+        best, second = best_second()
+        thr = _candidate_threshold((best & np.uint32(0xffffffc0)).view(f32), a_bound)
+        for i in range(len(q)):
+            blk = int(best[i] & np.uint32(63))
+            sval = (second[i:i + 1] & np.uint32(0xffffffc0)).view(f32)[0]
+            if not (sval > thr[i]):
+                cand = np.arange(nt)[~(d32(q[i:i + 1], t32)[0] > thr[i])]          # fallback: all targets
+            else:
+                idx = np.arange(blk * 32, min(nt, blk * 32 + 32))
+                dd = d32(q[i:i + 1], t32[idx])[0]
+                groups = {g for g in range(len(idx) // 4 + 1) if len(dd[4 * g:4 * g + 4]) and dd[4 * g:4 * g + 4].min() <= thr[i]}
+                cand = np.array([j for j in idx if (j - blk * 32) // 4 in groups])
+            got = cand[np.argmin(d64_all[r0 + i, cand])]
+            assert got == want[r0 + i], (kind, r0 + i, got, want[r0 + i])
+    rows = (ns + 31) // 32
+    if kind in ("lidar", "lidar_shifted"):
+        assert swept_total < 0.2 * rows * nblk            # ordered scans: most blocks are skipped
+
+
 def test_host_kabsch3_matches_lapack(tmp_path):
     """kabsch3.cuh (compiled for the host with g++) against the reference's SVD recipe."""
     src = tmp_path / "hk.cpp"
