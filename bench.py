@@ -350,25 +350,22 @@ def run_b200_arm(args):
     # the same kernel with the exhaustive sweep (every candidate evaluated; identical results):
     # the FP32-issue figure of the inner loop itself, timed the same way on a few launches
     exh_ms, exh_cand, exh_steps = 0.0, 0.0, min(args.steps, 6)
-    os.environ["B200ICP_SWEEP"] = "exhaustive"
-    try:
-        exh_res = None
-        for k in range(-1, exh_steps):
-            pl = pools[k % N_POOLS]
-            kev[max(k, 0)][0].record()
-            exh_res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
-                                           max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False)
-            kev[max(k, 0)][1].record()
-            torch.cuda.synchronize()
-            if k >= 0:
-                exh_ms += kev[k][0].elapsed_time(kev[k][1])
-                exh_cand += cand[k % N_POOLS]
-        same = results[(exh_steps - 1) % N_POOLS]
-        if not (torch.equal(exh_res.T, same.T) and torch.equal(exh_res.iters, same.iters)
-                and torch.equal(exh_res.error, same.error)):
-            raise RuntimeError("pruned and exhaustive sweeps disagree on the bench batch")
-    finally:
-        del os.environ["B200ICP_SWEEP"]
+    exh_res = None
+    for k in range(-1, exh_steps):
+        pl = pools[k % N_POOLS]
+        kev[max(k, 0)][0].record()
+        exh_res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
+                                       max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False,
+                                       flags=engine.FLAG_EXHAUSTIVE)
+        kev[max(k, 0)][1].record()
+        torch.cuda.synchronize()
+        if k >= 0:
+            exh_ms += kev[k][0].elapsed_time(kev[k][1])
+            exh_cand += cand[k % N_POOLS]
+    same = results[(exh_steps - 1) % N_POOLS]
+    if not (torch.allclose(exh_res.T, same.T, rtol=1e-11, atol=1e-11) and torch.equal(exh_res.iters, same.iters)
+            and torch.allclose(exh_res.error, same.error, rtol=1e-11, atol=0)):
+        raise RuntimeError("pruned and exhaustive sweeps disagree on the bench batch")
     clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
 
     # ---- timed region 2: end to end through the host-facing API ----

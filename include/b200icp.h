@@ -45,6 +45,24 @@ extern "C" {
 #define B200ICP_STATUS_NONPLANAR 5 /* 2-D entry given an init that moves points out of
                                       the plane; not run (use the 3-D entry)           */
 #define B200ICP_STATUS_SKIPPED 6   /* pair index < 0 (padding entry); not run         */
+#define B200ICP_STATUS_NOT_RESIDENT 7 /* gated launch: the pair's scans had not arrived
+                                      within the wait limit; not run (T = init, NaN error) */
+
+/* ---- launch flags (the `flags` argument of b200icp_run_ex and of the host entries) ---------
+ * Behaviour switches are arguments, not environment look-ups on the launch path.  (The
+ * developer overrides B200ICP_SWEEP=exhaustive, B200ICP_HOST_GATED=0, B200ICP_HOST_SLICES=n,
+ * B200ICP_PIPELINE_CHUNKS=n are read ONCE, when the library is loaded, and OR-ed into every
+ * call's flags.) */
+#define B200ICP_FLAG_EXHAUSTIVE 0x1u   /* evaluate every (source, target) candidate: no block
+                                          pruning.  Same results bit for bit; for A/B timing and as
+                                          the FP32-issue-rate figure of the inner loop.          */
+#define B200ICP_FLAG_NO_PRUNE 0x4u     /* the shipped row kernel with the block bounds switched off
+                                          (every block swept, same summation order: bit-identical
+                                          results); what the pruned == unpruned tests compare      */
+#define B200ICP_FLAG_HOST_CHUNKED 0x2u /* host entries: pair chunks alternating on two streams
+                                          instead of ONE gated launch (A/B)                     */
+#define B200ICP_FLAG_SLICES(n) (((unsigned)(n)&0xffu) << 8)  /* host entries: pool slices (0 = 24) */
+#define B200ICP_FLAG_CHUNKS(n) (((unsigned)(n)&0xffu) << 16) /* chunked host path: chunks (0 = 6)  */
 
 /* Library version (B200ICP_VERSION of the build). */
 int b200icp_version(void);
@@ -58,7 +76,7 @@ const char* b200icp_error_string(int code);
  * After a run of the planar kernel, bytes 8..15 of the workspace hold (uint64) the number of
  * (32 source points x 32 target points) tiles whose candidate distances were really evaluated --
  * the block-pruned sweep skips the tiles that provably hold no candidate (same results as the
- * exhaustive sweep; environment B200ICP_SWEEP=exhaustive, read at every launch, turns pruning off). */
+ * exhaustive sweep; B200ICP_FLAG_EXHAUSTIVE turns pruning off). */
 int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out);
 
 /* Batched point-to-point ICP.  Replaces, for every pair b independently,
@@ -105,7 +123,13 @@ int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_m
  * the kernel runs, and the kernel waits on it (system-scope acquire) before it stages a pair.
  * Everything else (counts, pairs, init, epsilon, normalize) must be resident at launch.
  * peer_pose_out / n_peers / peer_row0 as in b200icp_run_exchange (NULL, 0, 0: no exchange).  This is
- * how b200icp_run_host overlaps the upload of the pool with ONE launch over the whole pair list. */
+ * how b200icp_run_host overlaps the upload of the pool with ONE launch over the whole pair list.
+ * Wait limit: a pair whose scans have not become resident within 5 s of its turn is NOT run: it
+ * gets status B200ICP_STATUS_NOT_RESIDENT, T = its init and a NaN error (a stalled copy stream must
+ * neither hang the device nor produce poses from missing data), workspace word 5 (uint32 at byte
+ * 20) is set to 1, and every later pair whose scans are still missing is given up at once.  A
+ * caller that cannot tolerate missing pairs checks word 5 or the statuses (b200icp_run_host and
+ * lidar_slam_b200.engine do, and fail the call). */
 int b200icp_run_gated(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
                       const int32_t* pairs, const double* init, const double* epsilon,
                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
@@ -132,6 +156,42 @@ int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans
                          int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
                          double* const* peer_pose_out, int n_peers, long long peer_row0);
 
+/* The general device entry: b200icp_run with every optional extra in one signature.
+ * ready_scans     NULL, or the gate of b200icp_run_gated;
+ * peer_pose_out / n_peers / peer_row0   NULL, 0, 0, or the exchange of b200icp_run_exchange;
+ * flags           B200ICP_FLAG_* (0 = the shipped defaults).
+ * b200icp_run, b200icp_run_gated and b200icp_run_exchange are this entry with flags = 0. */
+int b200icp_run_ex(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                   const int32_t* pairs, const double* init, const double* epsilon,
+                   const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                   double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                   int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
+                   const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
+                   long long peer_row0, unsigned flags);
+
+/* b200icp_run_ex over a pool of RANGES instead of points (planar kernel only: n_beams <= 2048).
+ * Replaces get_lidar_data (modules/localization.py:252-307) AND run_icp (modules/icp.py:123-189)
+ * in one launch: the kernel builds the two scans of every pair itself -- beams with
+ * range_min <= r <= range_max kept in beam order (localization.py:288-290), x = r*cos(a) + off_x,
+ * y = r*sin(a) + off_y in the reference's operation order (localization.py:293-301; off = (0.13323, 0)),
+ * bit-identical to b200icp_scans_from_ranges -- so the pool costs 8 bytes per beam (4 with float32
+ * ranges) instead of 16 per point, in HBM and on the way there.
+ * ranges      [n_scans, n_beams] float64 (ranges_dtype 0) or float32 (ranges_dtype 1; exact when
+ *             every range is float32-representable, as Hokuyo millimetre data is: the caller checks).
+ * cos_tab / sin_tab [n_beams] float64: cos / sin of the beam angles evaluated by the caller (numpy).
+ * counts_out  [n_scans] int32 or NULL: valid beams of every scan that a pair referenced.
+ * corr_out    [n_pairs, n_max] int32 or NULL with n_max = n_beams rounded up to even.
+ * ready_scans NULL or the gate of b200icp_run_gated, counting resident RANGE rows.
+ * Everything else as b200icp_run_ex. */
+int b200icp_run_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
+                       const double* sin_tab, double range_min, double range_max, double off_x, double off_y,
+                       const int32_t* pairs, const double* init, const double* epsilon,
+                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                       int32_t* corr_out, int32_t* counts_out, void* workspace, size_t workspace_bytes,
+                       void* stream, const unsigned int* ready_scans, double* const* peer_pose_out,
+                       int n_peers, long long peer_row0, unsigned flags);
+
 /* b200icp_run for callers that live in HOST memory, like the reference (numpy arrays): every
  * pointer below is a host pointer (pinned or pageable), results included; the arguments mean
  * what they mean for b200icp_run.  The library owns the device side: a grow-only arena on the
@@ -148,6 +208,33 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
                      const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                      double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                      int32_t* corr_out);
+/* b200icp_run_host with the optional extras: the fused multi-GPU pose exchange
+ * (peer_pose_out / n_peers / peer_row0 as in b200icp_run_exchange: a HOST array of peer-mapped
+ * DEVICE pointers; NULL, 0, 0 = none) and the launch flags (B200ICP_FLAG_*).  With peers the same
+ * entry serves one and several GPUs: every rank calls it on its shard of the pair list. */
+int b200icp_run_host_ex(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                        const int32_t* pairs, const double* init, const double* epsilon,
+                        const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                        double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                        int32_t* corr_out, double* const* peer_pose_out, int n_peers, long long peer_row0,
+                        unsigned flags);
+
+/* b200icp_run_ranges for callers that live in HOST memory: the reference's pipeline
+ * get_lidar_data -> poses_from_scan_matching (modules/localization.py:252-307, then :95-134) with
+ * the synced lidar ranges [n_scans, n_beams] handed over as they are (float64, ranges_dtype 0; or a
+ * float32 copy, ranges_dtype 1).  Half (a quarter) of the bytes of the point pool cross PCIe; the
+ * range rows are streamed in slices under ONE gated launch whose kernel builds the scans
+ * (bit-identical to get_lidar_data) as it stages each pair.  All pointers are HOST pointers except
+ * the entries of peer_pose_out.  counts_out [n_scans] int32 or NULL: valid beams per scan (-1 for a
+ * scan no pair referenced).  Initial transforms must keep the plane (status 5 otherwise).
+ * Synchronous; calls on one device are serialised. */
+int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
+                            const double* sin_tab, double range_min, double range_max, double off_x, double off_y,
+                            const int32_t* pairs, const double* init, const double* epsilon,
+                            const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                            double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                            int32_t* corr_out, int32_t* counts_out, double* const* peer_pose_out, int n_peers,
+                            long long peer_row0, unsigned flags);
 int b200icp_host_release(void);
 
 /* One exact nearest-neighbour pass, exposed on its own for tests and for the

@@ -29,6 +29,21 @@ SIGNATURES = {
                                   c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_int,
                                   ctypes.c_longlong]),
+    "b200icp_run_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_int,
+                               ctypes.c_longlong, ctypes.c_uint]),
+    "b200icp_run_ranges": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double, c_double, c_double,
+                                   c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_double,
+                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                   c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, ctypes.c_uint]),
+    "b200icp_run_host_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_int, ctypes.c_longlong, ctypes.c_uint]),
+    "b200icp_run_host_ranges": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double, c_double,
+                                        c_double, c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                        c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_int, ctypes.c_longlong, ctypes.c_uint]),
     "b200icp_run_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),
@@ -54,6 +69,20 @@ SIGNATURES = {
                                       c_void_p]),
     "b200icp_texture_resolve": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
 }
+
+# launch flags (include/b200icp.h)
+FLAG_EXHAUSTIVE = 0x1
+FLAG_HOST_CHUNKED = 0x2
+FLAG_NO_PRUNE = 0x4
+
+
+def flag_slices(n: int) -> int:
+    return (int(n) & 0xff) << 8
+
+
+def flag_chunks(n: int) -> int:
+    return (int(n) & 0xff) << 16
+
 
 _lib = None
 

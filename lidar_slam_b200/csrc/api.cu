@@ -4,9 +4,24 @@
 #include <stdlib.h>
 
 #include "icp2d.cuh"
+#include "icp2d_rows.cuh"
 #include "icp3d.cuh"
 
 using namespace b200icp;
+
+// Developer overrides from the environment, read ONCE (first use) and OR-ed into every call's
+// flags; the launch path itself takes its switches as arguments (include/b200icp.h).
+unsigned b200icp::env_flags() {
+  static const unsigned f = [] {
+    unsigned v = 0;
+    if (const char* e = getenv("B200ICP_SWEEP")) if (e[0] == 'e' || e[0] == 'E') v |= B200ICP_FLAG_EXHAUSTIVE;
+    if (const char* e = getenv("B200ICP_HOST_GATED")) if (atoi(e) == 0) v |= B200ICP_FLAG_HOST_CHUNKED;
+    if (const char* e = getenv("B200ICP_HOST_SLICES")) { const int n = atoi(e); if (n >= 1 && n <= 255) v |= B200ICP_FLAG_SLICES(n); }
+    if (const char* e = getenv("B200ICP_PIPELINE_CHUNKS")) { const int n = atoi(e); if (n >= 1 && n <= 255) v |= B200ICP_FLAG_CHUNKS(n); }
+    return v;
+  }();
+  return f;
+}
 
 namespace {
 
@@ -36,13 +51,10 @@ DeviceInfo device_info() {
   return d;
 }
 
-// B200ICP_SWEEP=exhaustive selects the sweep that evaluates every (source, target) candidate
+// B200ICP_FLAG_EXHAUSTIVE selects the sweep that evaluates every (source, target) candidate
 // (same results; kept for A/B timing and as the FP32-issue-rate figure of the inner loop).
 // Default: the block-pruned sweep (icp2d.cuh).
-bool prune_enabled() {   // read at every launch, so a caller can switch between two launches
-  const char* e = getenv("B200ICP_SWEEP");
-  return !(e && (e[0] == 'e' || e[0] == 'E'));
-}
+inline bool prune_enabled(unsigned flags) { return !(flags & B200ICP_FLAG_EXHAUSTIVE); }
 
 template <int R, int W, int MINB, bool PRUNE>
 int launch2d_variant(const RunParams& p, cudaStream_t stream, int sms) {
@@ -58,10 +70,30 @@ int launch2d_variant(const RunParams& p, cudaStream_t stream, int sms) {
   kern<<<grid, W * 32, L.total, stream>>>(p);
   return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
 }
-template <int R, int W, int MINB>
-int launch2d(const RunParams& p, cudaStream_t stream, int sms) {
-  return prune_enabled() ? launch2d_variant<R, W, MINB, true>(p, stream, sms)
-                         : launch2d_variant<R, W, MINB, false>(p, stream, sms);
+
+// The shipped planar kernel (icp2d_rows.cuh): W warps per pair, R queries per lane.
+template <int W, int R, int MINB, bool PRUNE, bool RANGES>
+int launch_rows_variant(const RunParams& p, cudaStream_t stream, int sms) {
+  auto kern = icp2d_rows_kernel<W, R, MINB, PRUNE, RANGES>;
+  const Rows2dLayout L = rows2d_layout(p.n_max, W, RANGES);
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
+    return B200ICP_ERR_CUDA;
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, L.total) != cudaSuccess || per_sm < 1)
+    return B200ICP_ERR_CUDA;
+  const long long resident = (long long)per_sm * sms;
+  const int grid = (int)(p.n_pairs < resident ? p.n_pairs : resident);
+  kern<<<grid, W * 32, L.total, stream>>>(p);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+template <int W, int R, int MINB>
+int launch_rows(const RunParams& p, cudaStream_t stream, int sms, unsigned flags) {
+  const bool prune = !(flags & B200ICP_FLAG_NO_PRUNE);
+  if (p.ranges)
+    return prune ? launch_rows_variant<W, R, MINB, true, true>(p, stream, sms)
+                 : launch_rows_variant<W, R, MINB, false, true>(p, stream, sms);
+  return prune ? launch_rows_variant<W, R, MINB, true, false>(p, stream, sms)
+               : launch_rows_variant<W, R, MINB, false, false>(p, stream, sms);
 }
 
 int launch3d(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, int sms) {
@@ -106,28 +138,31 @@ int launch3d(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
   return B200ICP_ERR_CUDA;
 }
 
-int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
-  if (!p.scans || !p.counts || !p.pairs || p.n_scans <= 0 || p.n_max <= 0 || p.n_pairs < 0 ||
+int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, unsigned flags) {
+  flags |= b200icp::env_flags();
+  if ((!p.ranges && (!p.scans || !p.counts)) || !p.pairs || p.n_scans <= 0 || p.n_max <= 0 || p.n_pairs < 0 ||
       (dim != 2 && dim != 3))
     return B200ICP_ERR_BAD_ARG;
   if (p.n_pairs == 0) return B200ICP_OK;
   if (!workspace || workspace_bytes < 256) return B200ICP_ERR_WORKSPACE;
-  if ((reinterpret_cast<uintptr_t>(p.scans) & 15u) != 0) return B200ICP_ERR_BAD_ARG;
+  if (!p.ranges && (reinterpret_cast<uintptr_t>(p.scans) & 15u) != 0) return B200ICP_ERR_BAD_ARG;
   const DeviceInfo d = device_info();
   if (!d.ok) return B200ICP_ERR_NO_DEVICE;
   p.queue = reinterpret_cast<unsigned int*>(workspace);
   if (cudaMemsetAsync(workspace, 0, 256, stream) != cudaSuccess) return B200ICP_ERR_CUDA;
   if (dim == 2 && p.n_max <= kMax2d) {
-    // W warps, up to R rows of 32 source points per warp: capacity 32*R*W >= n_max
-    if (p.n_max <= 256) return launch2d<2, 4, 8>(p, stream, d.sms);
-    if (p.n_max <= 512) return launch2d<4, 4, 6>(p, stream, d.sms);
-    if (p.n_max <= 1280) {
-      // pruned kernel: 64 registers, 4 CTAs/SM (it is latency-bound: +5 % over 3 CTAs, measured);
-      // exhaustive kernel: 80 registers, 3 CTAs/SM (FMA-bound, spills would sit in the sweep)
-      return prune_enabled() ? launch2d_variant<5, 8, 4, true>(p, stream, d.sms)
-                             : launch2d_variant<5, 8, 3, false>(p, stream, d.sms);
+    if (!(flags & B200ICP_FLAG_EXHAUSTIVE) || p.ranges) {
+      // row kernel: rows of 32*R source points per warp step; capacity is not a function of W
+      if (p.n_max <= 512) return launch_rows<4, 1, 5>(p, stream, d.sms, flags);
+      if (p.n_max <= 1280) return launch_rows<4, 2, 4>(p, stream, d.sms, flags);
+      return launch_rows<8, 2, 2>(p, stream, d.sms, flags);
     }
-    return launch2d<8, 8, 2>(p, stream, d.sms);
+    // exhaustive register-tiled kernel (round 1): W warps, up to R rows of 32 source points per
+    // warp: capacity 32*R*W >= n_max; 80 registers, 3 CTAs/SM at 1081 points (FMA-bound)
+    if (p.n_max <= 256) return launch2d_variant<2, 4, 8, false>(p, stream, d.sms);
+    if (p.n_max <= 512) return launch2d_variant<4, 4, 6, false>(p, stream, d.sms);
+    if (p.n_max <= 1280) return launch2d_variant<5, 8, 3, false>(p, stream, d.sms);
+    return launch2d_variant<8, 8, 2, false>(p, stream, d.sms);
   }
   return launch3d(p, dim, workspace, workspace_bytes, stream, d.sms);
 }
@@ -196,7 +231,7 @@ static int run_common(const double* scans, const int32_t* counts, int n_scans, i
                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                       int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
                       double* const* peer_pose_out, int n_peers, long long peer_row0,
-                      const unsigned int* ready_scans = nullptr) {
+                      const unsigned int* ready_scans = nullptr, unsigned flags = 0) {
   if (!init || !epsilon || !normalize || !T_out || max_iters < 0) return B200ICP_ERR_BAD_ARG;
   if (ready_scans && uses_general_kernel(n_max, dim)) return B200ICP_ERR_BAD_ARG;   // planar kernel only
   if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && !peer_pose_out) || peer_row0 < 0)
@@ -209,11 +244,54 @@ static int run_common(const double* scans, const int32_t* counts, int n_scans, i
   p.corr_out = corr_out; p.dist2_out = nullptr; p.nearest_only = 0;
   p.n_peers = n_peers; p.peer_row0 = peer_row0;
   p.ready_scans = ready_scans;
+  p.gate_timeout_ns = 5000000000ull;
   for (int k = 0; k < n_peers; ++k) {
     if (!peer_pose_out[k] || (reinterpret_cast<uintptr_t>(peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
     p.peer_out[k] = peer_pose_out[k];
   }
-  return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+  return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream), flags);
+}
+
+int b200icp_run_ex(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                   const int32_t* pairs, const double* init, const double* epsilon,
+                   const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                   double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                   int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
+                   const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
+                   long long peer_row0, unsigned flags) {
+  return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
+                    stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
+                    workspace_bytes, stream, peer_pose_out, n_peers, peer_row0, ready_scans, flags);
+}
+
+int b200icp_run_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
+                       const double* sin_tab, double range_min, double range_max, double off_x, double off_y,
+                       const int32_t* pairs, const double* init, const double* epsilon,
+                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                       int32_t* corr_out, int32_t* counts_out, void* workspace, size_t workspace_bytes,
+                       void* stream, const unsigned int* ready_scans, double* const* peer_pose_out,
+                       int n_peers, long long peer_row0, unsigned flags) {
+  if (!ranges || (ranges_dtype != 0 && ranges_dtype != 1) || !cos_tab || !sin_tab || n_beams <= 0 ||
+      n_beams > kMax2d || !init || !epsilon || !normalize || !T_out || max_iters < 0)
+    return B200ICP_ERR_BAD_ARG;
+  if ((reinterpret_cast<uintptr_t>(ranges) & (ranges_dtype ? 3u : 7u)) != 0) return B200ICP_ERR_BAD_ARG;
+  if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && !peer_pose_out) || peer_row0 < 0)
+    return B200ICP_ERR_BAD_ARG;
+  RunParams p{};
+  p.ranges = ranges; p.ranges_f32 = ranges_dtype; p.n_beams = n_beams; p.cos_tab = cos_tab; p.sin_tab = sin_tab;
+  p.range_min = range_min; p.range_max = range_max; p.off_x = off_x; p.off_y = off_y; p.counts_out = counts_out;
+  p.n_scans = n_scans; p.n_max = n_beams + (n_beams & 1);
+  p.pairs = pairs; p.init = init; p.epsilon = epsilon; p.normalize = normalize;
+  p.n_pairs = n_pairs; p.max_iters = max_iters; p.stopping_thresh = stopping_thresh;
+  p.T_out = T_out; p.err_out = err_out; p.iters_out = iters_out; p.status_out = status_out;
+  p.corr_out = corr_out; p.n_peers = n_peers; p.peer_row0 = peer_row0;
+  p.ready_scans = ready_scans; p.gate_timeout_ns = 5000000000ull;
+  for (int k = 0; k < n_peers; ++k) {
+    if (!peer_pose_out[k] || (reinterpret_cast<uintptr_t>(peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
+    p.peer_out[k] = peer_pose_out[k];
+  }
+  return dispatch(p, 2, workspace, workspace_bytes, static_cast<cudaStream_t>(stream), flags);
 }
 
 int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
@@ -258,7 +336,7 @@ int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int
   p.scans = scans; p.counts = counts; p.n_scans = n_scans; p.n_max = n_max;
   p.pairs = pairs; p.n_pairs = n_pairs; p.max_iters = 0; p.stopping_thresh = 0.0;
   p.corr_out = corr_out; p.dist2_out = dist2_out; p.nearest_only = 1;
-  return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+  return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream), 0);
 }
 
 int b200icp_pack_poses(const double* T, const double* err, int n, double* out, void* stream) {

@@ -1,22 +1,25 @@
-// Host-buffer entry of the ICP path: what a numpy caller of the reference binds directly.
+// Host-buffer entries of the ICP path: what a numpy caller of the reference binds directly.
 //
-//   b200icp_run_host   run_icp for a batch, HOST pointers in and out   modules/icp.py:123-189
-//                      (the loops of modules/localization.py:112-130, main.py:161-172,
-//                       code/icp_warm_up/test_icp.py:70-91 handed over as one pair list)
+//   b200icp_run_host[_ex]     run_icp for a batch, HOST pointers in and out   modules/icp.py:123-189
+//                             (the loops of modules/localization.py:112-130, main.py:161-172,
+//                              code/icp_warm_up/test_icp.py:70-91 handed over as one pair list)
+//   b200icp_run_host_ranges   the same with the lidar RANGES as input: get_lidar_data
+//                             (modules/localization.py:252-307) + run_icp in one launch, half the
+//                             bytes over PCIe (a quarter with float32 ranges)
 //
-// The reference works on numpy arrays in host memory, so this entry owns the device side: a
-// grow-only arena per device, a copy stream and two compute streams.  The scan pool is streamed
-// to the device in slices while the pair list runs in chunks: before chunk c starts, the prefix
-// of the pool its pairs reference is resident (consecutive pairs (i, i-1) need the pool in
-// order, so copy and compute overlap; arbitrary pair lists simply wait for more of the pool).
-// Planar batches take the GATED path instead of chunks: the pool is enqueued in slices on the copy
-// stream, each slice followed by a 4-byte copy that raises a device-side counter of resident scans;
-// ONE persistent kernel launch over the whole pair list is issued right behind them on a compute
-// stream (it only depends on the small inputs) and waits (ld.acquire.sys) on that counter before it
-// stages a pair.  No per-chunk
-// launch tails, copy and compute overlap down to the slice.
-// Results come back with one set of device-to-host copies at the end.  The call is synchronous.
+// The reference works on numpy arrays in host memory, so these entries own the device side: a
+// grow-only arena per device, a copy stream and two compute streams.  Planar batches take the
+// GATED path: the pool (points or range rows) is enqueued in slices on the copy stream, each slice
+// followed by a 4-byte copy that raises a device-side counter of resident rows; ONE persistent
+// kernel launch over the whole pair list is issued right behind them on a compute stream (it only
+// depends on the small inputs) and waits (ld.acquire.sys) on that counter before it stages a pair:
+// no per-chunk launch tails, copy and compute overlap down to the slice.  Other batches (3-D clouds,
+// initial transforms that leave the plane, small batches) run in chunks of the pair list: before
+// chunk c starts, the prefix of the pool its pairs reference is resident.
+// Results come back with one set of device-to-host copies at the end.  The calls are synchronous.
 // Pinned host memory makes the copies asynchronous and faster; pageable memory works too.
+// With peer buffers (multi-GPU) the kernel's epilogue also stores every finished pose row into
+// every rank's gather buffer (b200icp_run_exchange), so the same entry serves 1 and N GPUs.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -24,6 +27,8 @@
 #include <mutex>
 
 #include "../../include/b200icp.h"
+
+namespace b200icp { unsigned env_flags(); }
 
 namespace {
 
@@ -37,7 +42,7 @@ struct HostArena {
   size_t cap = 0;
   cudaStream_t copy = nullptr, comp[2] = {nullptr, nullptr};
   cudaEvent_t ready[kMaxChunks] = {}, done[2] = {nullptr, nullptr}, small = nullptr;
-  unsigned int* progress_host = nullptr;   // pinned: cumulative scan counts, one per slice
+  unsigned int* progress_host = nullptr;   // pinned: cumulative row counts, one per slice (+ the gave-up word)
   bool ok = false;
 };
 
@@ -83,162 +88,192 @@ bool keeps_plane(const double* T) {
 
 #define B200_TRY(expr) do { if ((expr) != cudaSuccess) { cudaGetLastError(); return B200ICP_ERR_CUDA; } } while (0)
 
-}  // namespace
-
-extern "C" {
-
-int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
-                     const int32_t* pairs, const double* init, const double* epsilon,
-                     const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
-                     double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
-                     int32_t* corr_out) {
-  if (!scans || !counts || !pairs || !init || !epsilon || !normalize || !T_out || n_scans <= 0 ||
-      n_max <= 0 || n_pairs < 0 || max_iters < 0 || (dim != 2 && dim != 3) || ((size_t)n_max * dim) % 2 != 0)
-    return B200ICP_ERR_BAD_ARG;
-  if (n_pairs == 0) return B200ICP_OK;
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return B200ICP_ERR_NO_DEVICE; }
-  std::lock_guard<std::mutex> lock(g_mutex);
-  HostArena& a = g_arena[dev];
-  if (!arena_init(a)) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
-
-  // An initial transform that leaves the plane: the reference lifts the scans to z = 0 and carries
-  // on in 3-D (icp.py:153-156), so the whole batch goes through the general kernel on a z-padded pool.
-  int run_dim = dim;
-  if (dim == 2)
-    for (int b = 0; b < n_pairs; ++b)
-      if (!keeps_plane(init + (size_t)b * 16)) { run_dim = 3; break; }
-
-  bool gated = run_dim == 2 && n_max <= kMax2dPoints && n_pairs >= kPipelineMinPairs;
-  if (const char* e = getenv("B200ICP_HOST_GATED")) gated = gated && atoi(e) != 0;   // 0: chunked path (A/B)
-  if (gated) {
-    Carver cv;
-    const size_t row_bytes = (size_t)n_max * 2 * sizeof(double);
-    const size_t o_scans = cv.take((size_t)n_scans * row_bytes);
-    const size_t o_counts = cv.take((size_t)n_scans * 4);
-    const size_t o_pairs = cv.take((size_t)n_pairs * 8);
-    const size_t o_init = cv.take((size_t)n_pairs * 128);
-    const size_t o_eps = cv.take((size_t)n_pairs * 8);
-    const size_t o_norm = cv.take((size_t)n_pairs);
-    const size_t o_T = cv.take((size_t)n_pairs * 128);
-    const size_t o_err = cv.take((size_t)n_pairs * 8);
-    const size_t o_iters = cv.take((size_t)n_pairs * 4);
-    const size_t o_status = cv.take((size_t)n_pairs * 4);
-    const size_t o_corr = corr_out ? cv.take((size_t)n_pairs * n_max * 4) : 0;
-    const size_t o_flag = cv.take(256);
-    size_t ws_bytes = 0;
-    const int rcw = b200icp_workspace_bytes(n_pairs, n_max, 2, &ws_bytes);
-    if (rcw != B200ICP_OK) return rcw;
-    const size_t o_ws = cv.take(ws_bytes);
-    if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
-    char* d = a.base;
-    B200_TRY(cudaMemsetAsync(d + o_flag, 0, 256, a.copy));
-    B200_TRY(cudaMemcpyAsync(d + o_counts, counts, (size_t)n_scans * 4, cudaMemcpyHostToDevice, a.copy));
-    B200_TRY(cudaMemcpyAsync(d + o_pairs, pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
-    B200_TRY(cudaMemcpyAsync(d + o_init, init, (size_t)n_pairs * 128, cudaMemcpyHostToDevice, a.copy));
-    B200_TRY(cudaMemcpyAsync(d + o_eps, epsilon, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
-    B200_TRY(cudaMemcpyAsync(d + o_norm, normalize, (size_t)n_pairs, cudaMemcpyHostToDevice, a.copy));
-    B200_TRY(cudaEventRecord(a.small, a.copy));
-    B200_TRY(cudaStreamWaitEvent(a.comp[0], a.small, 0));
-    // The slices are ENQUEUED before the launch: if something serialises launches (a profiler,
-    // CUDA_LAUNCH_BLOCKING) the kernel must never wait for a copy the host has not issued yet.
-    int n_slices = 24;
-    if (const char* e = getenv("B200ICP_HOST_SLICES")) { const int v = atoi(e); if (v >= 1) n_slices = v; }
-    if (n_slices > kMaxSlices - 1) n_slices = kMaxSlices - 1;   // the last pinned word receives the gave-up flag
-    if (n_slices > n_scans) n_slices = n_scans;
-    int copied = 0;
-    bool copy_ok = true;
-    for (int c = 0; c < n_slices && copy_ok; ++c) {
-      const int upto = (int)((long long)n_scans * (c + 1) / n_slices);
-      if (upto > copied)
-        copy_ok = cudaMemcpyAsync(d + o_scans + (size_t)copied * row_bytes, scans + (size_t)copied * n_max * 2,
-                                  (size_t)(upto - copied) * row_bytes, cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
-      copied = upto;
-      a.progress_host[c] = (unsigned int)copied;
-      copy_ok = copy_ok && cudaMemcpyAsync(d + o_flag, a.progress_host + c, sizeof(unsigned int),
-                                           cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
-    }
-    if (!copy_ok) {
-      cudaGetLastError();
-      cudaStreamSynchronize(a.copy);
-      cudaGetLastError();
-      return B200ICP_ERR_CUDA;
-    }
-    const int rc_run = b200icp_run_gated(
-        reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts), n_scans, n_max,
-        2, reinterpret_cast<const int32_t*>(d + o_pairs), reinterpret_cast<const double*>(d + o_init),
-        reinterpret_cast<const double*>(d + o_eps), reinterpret_cast<const uint8_t*>(d + o_norm), n_pairs, max_iters,
-        stopping_thresh, reinterpret_cast<double*>(d + o_T), reinterpret_cast<double*>(d + o_err),
-        reinterpret_cast<int32_t*>(d + o_iters), reinterpret_cast<int32_t*>(d + o_status),
-        corr_out ? reinterpret_cast<int32_t*>(d + o_corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
-        reinterpret_cast<const unsigned int*>(d + o_flag), nullptr, 0, 0);
-    B200_TRY(cudaEventRecord(a.done[0], a.comp[0]));
-    B200_TRY(cudaStreamWaitEvent(a.copy, a.done[0], 0));
-    if (rc_run == B200ICP_OK) {
-      B200_TRY(cudaMemcpyAsync(T_out, d + o_T, (size_t)n_pairs * 128, cudaMemcpyDeviceToHost, a.copy));
-      if (err_out) B200_TRY(cudaMemcpyAsync(err_out, d + o_err, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, a.copy));
-      if (iters_out) B200_TRY(cudaMemcpyAsync(iters_out, d + o_iters, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
-      if (status_out) B200_TRY(cudaMemcpyAsync(status_out, d + o_status, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
-      if (corr_out) B200_TRY(cudaMemcpyAsync(corr_out, d + o_corr, (size_t)n_pairs * n_max * 4, cudaMemcpyDeviceToHost, a.copy));
-      // workspace word 5: the kernel gave up waiting for the pool (never expected; results void)
-      B200_TRY(cudaMemcpyAsync(a.progress_host + kMaxSlices - 1, d + o_ws + 20, sizeof(unsigned int),
-                               cudaMemcpyDeviceToHost, a.copy));
-    }
-    B200_TRY(cudaStreamSynchronize(a.copy));
-    if (rc_run == B200ICP_OK && a.progress_host[kMaxSlices - 1] != 0u) return B200ICP_ERR_CUDA;
-    return rc_run;
+// The pool a host call works on: points [n_scans, n_max, dim] float64, or ranges [n_scans, n_beams].
+struct HostPool {
+  const void* data;
+  int kind;                 // 0: points, 1: ranges float64, 2: ranges float32
+  int n_scans, n_max, dim;  // ranges: n_max = n_beams rounded up to even, dim = 2
+  int n_beams;
+  const int32_t* counts;    // points only
+  const double *cos_tab, *sin_tab;
+  double range_min, range_max, off_x, off_y;
+  int32_t* counts_out;      // ranges only, host, may be null
+  size_t row_bytes() const {
+    return kind == 0 ? (size_t)n_max * dim * sizeof(double) : (size_t)n_beams * (kind == 1 ? 8 : 4);
   }
+};
 
-  // chunks of the pair list and the pool prefix each one needs
+struct HostIo {
+  const int32_t* pairs; const double* init; const double* epsilon; const uint8_t* normalize;
+  int n_pairs, max_iters; double stopping_thresh;
+  double* T_out; double* err_out; int32_t* iters_out; int32_t* status_out; int32_t* corr_out;
+  double* const* peers; int n_peers; long long peer_row0;
+  unsigned flags;
+};
+
+struct SmallOffsets { size_t pairs, init, eps, norm, T, err, iters, status, corr; };
+
+SmallOffsets carve_small(Carver& cv, const HostIo& io, int n_max) {
+  SmallOffsets o{};
+  o.pairs = cv.take((size_t)io.n_pairs * 8);
+  o.init = cv.take((size_t)io.n_pairs * 128);
+  o.eps = cv.take((size_t)io.n_pairs * 8);
+  o.norm = cv.take((size_t)io.n_pairs);
+  o.T = cv.take((size_t)io.n_pairs * 128);
+  o.err = cv.take((size_t)io.n_pairs * 8);
+  o.iters = cv.take((size_t)io.n_pairs * 4);
+  o.status = cv.take((size_t)io.n_pairs * 4);
+  o.corr = io.corr_out ? cv.take((size_t)io.n_pairs * n_max * 4) : 0;
+  return o;
+}
+
+int upload_small(HostArena& a, char* d, const SmallOffsets& o, const HostIo& io) {
+  B200_TRY(cudaMemcpyAsync(d + o.pairs, io.pairs, (size_t)io.n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
+  B200_TRY(cudaMemcpyAsync(d + o.init, io.init, (size_t)io.n_pairs * 128, cudaMemcpyHostToDevice, a.copy));
+  B200_TRY(cudaMemcpyAsync(d + o.eps, io.epsilon, (size_t)io.n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
+  B200_TRY(cudaMemcpyAsync(d + o.norm, io.normalize, (size_t)io.n_pairs, cudaMemcpyHostToDevice, a.copy));
+  return B200ICP_OK;
+}
+
+int download_results(HostArena& a, char* d, const SmallOffsets& o, const HostIo& io, int n_max) {
+  const size_t n = (size_t)io.n_pairs;
+  B200_TRY(cudaMemcpyAsync(io.T_out, d + o.T, n * 128, cudaMemcpyDeviceToHost, a.copy));
+  if (io.err_out) B200_TRY(cudaMemcpyAsync(io.err_out, d + o.err, n * 8, cudaMemcpyDeviceToHost, a.copy));
+  if (io.iters_out) B200_TRY(cudaMemcpyAsync(io.iters_out, d + o.iters, n * 4, cudaMemcpyDeviceToHost, a.copy));
+  if (io.status_out) B200_TRY(cudaMemcpyAsync(io.status_out, d + o.status, n * 4, cudaMemcpyDeviceToHost, a.copy));
+  if (io.corr_out) B200_TRY(cudaMemcpyAsync(io.corr_out, d + o.corr, n * n_max * 4, cudaMemcpyDeviceToHost, a.copy));
+  return B200ICP_OK;
+}
+
+// ONE gated launch over the whole pair list while the pool arrives in slices (planar kernel).
+int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
+  Carver cv;
+  const size_t row_bytes = pool.row_bytes();
+  const size_t o_pool = cv.take((size_t)pool.n_scans * row_bytes);
+  const size_t o_counts = cv.take((size_t)pool.n_scans * 4);
+  const size_t o_tabs = pool.kind ? cv.take((size_t)pool.n_beams * 16) : 0;
+  const SmallOffsets o = carve_small(cv, io, pool.n_max);
+  const size_t o_flag = cv.take(256);
+  size_t ws_bytes = 0;
+  const int rcw = b200icp_workspace_bytes(io.n_pairs, pool.n_max, 2, &ws_bytes);
+  if (rcw != B200ICP_OK) return rcw;
+  const size_t o_ws = cv.take(ws_bytes);
+  if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
+  char* d = a.base;
+  B200_TRY(cudaMemsetAsync(d + o_flag, 0, 256, a.copy));
+  if (pool.kind == 0) {
+    B200_TRY(cudaMemcpyAsync(d + o_counts, pool.counts, (size_t)pool.n_scans * 4, cudaMemcpyHostToDevice, a.copy));
+  } else {
+    B200_TRY(cudaMemcpyAsync(d + o_tabs, pool.cos_tab, (size_t)pool.n_beams * 8, cudaMemcpyHostToDevice, a.copy));
+    B200_TRY(cudaMemcpyAsync(d + o_tabs + (size_t)pool.n_beams * 8, pool.sin_tab, (size_t)pool.n_beams * 8,
+                             cudaMemcpyHostToDevice, a.copy));
+    if (pool.counts_out) B200_TRY(cudaMemsetAsync(d + o_counts, 0xff, (size_t)pool.n_scans * 4, a.copy));   // -1: not referenced
+  }
+  const int rc_up = upload_small(a, d, o, io);
+  if (rc_up != B200ICP_OK) return rc_up;
+  B200_TRY(cudaEventRecord(a.small, a.copy));
+  B200_TRY(cudaStreamWaitEvent(a.comp[0], a.small, 0));
+  // The slices are ENQUEUED before the launch: if something serialises launches (a profiler,
+  // CUDA_LAUNCH_BLOCKING) the kernel must never wait for a copy the host has not issued yet.
+  int n_slices = (int)((io.flags >> 8) & 0xffu);
+  if (n_slices == 0) n_slices = 24;
+  if (n_slices > kMaxSlices - 1) n_slices = kMaxSlices - 1;   // the last pinned word receives the gave-up flag
+  if (n_slices > pool.n_scans) n_slices = pool.n_scans;
+  int copied = 0;
+  bool copy_ok = true;
+  const char* src = static_cast<const char*>(pool.data);
+  for (int c = 0; c < n_slices && copy_ok; ++c) {
+    const int upto = (int)((long long)pool.n_scans * (c + 1) / n_slices);
+    if (upto > copied)
+      copy_ok = cudaMemcpyAsync(d + o_pool + (size_t)copied * row_bytes, src + (size_t)copied * row_bytes,
+                                (size_t)(upto - copied) * row_bytes, cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
+    copied = upto;
+    a.progress_host[c] = (unsigned int)copied;
+    copy_ok = copy_ok && cudaMemcpyAsync(d + o_flag, a.progress_host + c, sizeof(unsigned int),
+                                         cudaMemcpyHostToDevice, a.copy) == cudaSuccess;
+  }
+  if (!copy_ok) {
+    cudaGetLastError();
+    cudaStreamSynchronize(a.copy);
+    cudaGetLastError();
+    return B200ICP_ERR_CUDA;
+  }
+  int rc_run;
+  if (pool.kind == 0) {
+    rc_run = b200icp_run_ex(
+        reinterpret_cast<const double*>(d + o_pool), reinterpret_cast<const int32_t*>(d + o_counts), pool.n_scans,
+        pool.n_max, 2, reinterpret_cast<const int32_t*>(d + o.pairs), reinterpret_cast<const double*>(d + o.init),
+        reinterpret_cast<const double*>(d + o.eps), reinterpret_cast<const uint8_t*>(d + o.norm), io.n_pairs,
+        io.max_iters, io.stopping_thresh, reinterpret_cast<double*>(d + o.T), reinterpret_cast<double*>(d + o.err),
+        reinterpret_cast<int32_t*>(d + o.iters), reinterpret_cast<int32_t*>(d + o.status),
+        io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
+        reinterpret_cast<const unsigned int*>(d + o_flag), io.peers, io.n_peers, io.peer_row0, io.flags);
+  } else {
+    rc_run = b200icp_run_ranges(
+        d + o_pool, pool.kind == 2 ? 1 : 0, pool.n_scans, pool.n_beams, reinterpret_cast<const double*>(d + o_tabs),
+        reinterpret_cast<const double*>(d + o_tabs) + pool.n_beams, pool.range_min, pool.range_max, pool.off_x,
+        pool.off_y, reinterpret_cast<const int32_t*>(d + o.pairs), reinterpret_cast<const double*>(d + o.init),
+        reinterpret_cast<const double*>(d + o.eps), reinterpret_cast<const uint8_t*>(d + o.norm), io.n_pairs,
+        io.max_iters, io.stopping_thresh, reinterpret_cast<double*>(d + o.T), reinterpret_cast<double*>(d + o.err),
+        reinterpret_cast<int32_t*>(d + o.iters), reinterpret_cast<int32_t*>(d + o.status),
+        io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) : nullptr,
+        pool.counts_out ? reinterpret_cast<int32_t*>(d + o_counts) : nullptr, d + o_ws, ws_bytes, a.comp[0],
+        reinterpret_cast<const unsigned int*>(d + o_flag), io.peers, io.n_peers, io.peer_row0, io.flags);
+  }
+  B200_TRY(cudaEventRecord(a.done[0], a.comp[0]));
+  B200_TRY(cudaStreamWaitEvent(a.copy, a.done[0], 0));
+  if (rc_run == B200ICP_OK) {
+    const int rc_dn = download_results(a, d, o, io, pool.n_max);
+    if (rc_dn != B200ICP_OK) return rc_dn;
+    if (pool.kind && pool.counts_out)
+      B200_TRY(cudaMemcpyAsync(pool.counts_out, d + o_counts, (size_t)pool.n_scans * 4, cudaMemcpyDeviceToHost, a.copy));
+    // workspace word 5: the kernel gave up waiting for the pool (never expected; those pairs were not run)
+    B200_TRY(cudaMemcpyAsync(a.progress_host + kMaxSlices - 1, d + o_ws + 20, sizeof(unsigned int),
+                             cudaMemcpyDeviceToHost, a.copy));
+  }
+  B200_TRY(cudaStreamSynchronize(a.copy));
+  if (rc_run == B200ICP_OK && a.progress_host[kMaxSlices - 1] != 0u) return B200ICP_ERR_CUDA;
+  return rc_run;
+}
+
+// Chunks of the pair list on two compute streams; each chunk waits for the pool prefix it references.
+int run_chunked(HostArena& a, const HostPool& pool, const HostIo& io, int run_dim) {
   int n_chunks = 1;
-  if (n_pairs >= kPipelineMinPairs && run_dim == dim) {
-    n_chunks = 6;
-    if (const char* e = getenv("B200ICP_PIPELINE_CHUNKS")) { const int v = atoi(e); if (v >= 1) n_chunks = v; }
+  if (io.n_pairs >= kPipelineMinPairs && run_dim == pool.dim) {
+    n_chunks = (int)((io.flags >> 16) & 0xffu);
+    if (n_chunks == 0) n_chunks = 6;
     if (n_chunks > kMaxChunks) n_chunks = kMaxChunks;
   }
   int lo[kMaxChunks + 1], need[kMaxChunks];
-  for (int c = 0; c <= n_chunks; ++c) lo[c] = (int)((long long)n_pairs * c / n_chunks);
+  for (int c = 0; c <= n_chunks; ++c) lo[c] = (int)((long long)io.n_pairs * c / n_chunks);
   for (int c = 0; c < n_chunks; ++c) {
     int m = -1;
     for (int b = lo[c]; b < lo[c + 1]; ++b) {
-      const int s = pairs[2 * b], t = pairs[2 * b + 1];
+      const int s = io.pairs[2 * b], t = io.pairs[2 * b + 1];
       if (s > m) m = s;
       if (t > m) m = t;
     }
-    need[c] = (c == n_chunks - 1) ? n_scans : (m + 1 < 0 ? 0 : (m + 1 > n_scans ? n_scans : m + 1));
+    need[c] = (c == n_chunks - 1) ? pool.n_scans : (m + 1 < 0 ? 0 : (m + 1 > pool.n_scans ? pool.n_scans : m + 1));
   }
-
-  // arena layout
-  size_t ws_bytes[kMaxChunks];
+  size_t ws_bytes[kMaxChunks], o_ws[kMaxChunks];
   Carver cv;
-  const size_t row_bytes = (size_t)n_max * run_dim * sizeof(double);
-  const size_t o_scans = cv.take((size_t)n_scans * row_bytes);
-  const size_t o_counts = cv.take((size_t)n_scans * 4);
-  const size_t o_pairs = cv.take((size_t)n_pairs * 8);
-  const size_t o_init = cv.take((size_t)n_pairs * 128);
-  const size_t o_eps = cv.take((size_t)n_pairs * 8);
-  const size_t o_norm = cv.take((size_t)n_pairs);
-  const size_t o_T = cv.take((size_t)n_pairs * 128);
-  const size_t o_err = cv.take((size_t)n_pairs * 8);
-  const size_t o_iters = cv.take((size_t)n_pairs * 4);
-  const size_t o_status = cv.take((size_t)n_pairs * 4);
-  const size_t o_corr = corr_out ? cv.take((size_t)n_pairs * n_max * 4) : 0;
-  size_t o_ws[kMaxChunks];
+  const size_t row_bytes = (size_t)pool.n_max * run_dim * sizeof(double);
+  const size_t o_scans = cv.take((size_t)pool.n_scans * row_bytes);
+  const size_t o_counts = cv.take((size_t)pool.n_scans * 4);
+  const SmallOffsets o = carve_small(cv, io, pool.n_max);
   for (int c = 0; c < n_chunks; ++c) {
-    const int rc = b200icp_workspace_bytes(lo[c + 1] - lo[c], n_max, run_dim, &ws_bytes[c]);
+    const int rc = b200icp_workspace_bytes(lo[c + 1] - lo[c], pool.n_max, run_dim, &ws_bytes[c]);
     if (rc != B200ICP_OK) return rc;
     o_ws[c] = cv.take(ws_bytes[c]);
   }
   if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
   char* d = a.base;
+  const double* scans = static_cast<const double*>(pool.data);
 
-  // small inputs first
-  B200_TRY(cudaMemcpyAsync(d + o_counts, counts, (size_t)n_scans * 4, cudaMemcpyHostToDevice, a.copy));
-  B200_TRY(cudaMemcpyAsync(d + o_pairs, pairs, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
-  B200_TRY(cudaMemcpyAsync(d + o_init, init, (size_t)n_pairs * 128, cudaMemcpyHostToDevice, a.copy));
-  B200_TRY(cudaMemcpyAsync(d + o_eps, epsilon, (size_t)n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
-  B200_TRY(cudaMemcpyAsync(d + o_norm, normalize, (size_t)n_pairs, cudaMemcpyHostToDevice, a.copy));
-  if (run_dim != dim) B200_TRY(cudaMemsetAsync(d + o_scans, 0, (size_t)n_scans * row_bytes, a.copy));
+  B200_TRY(cudaMemcpyAsync(d + o_counts, pool.counts, (size_t)pool.n_scans * 4, cudaMemcpyHostToDevice, a.copy));
+  const int rc_up = upload_small(a, d, o, io);
+  if (rc_up != B200ICP_OK) return rc_up;
+  if (run_dim != pool.dim) B200_TRY(cudaMemsetAsync(d + o_scans, 0, (size_t)pool.n_scans * row_bytes, a.copy));
   B200_TRY(cudaEventRecord(a.small, a.copy));
   B200_TRY(cudaStreamWaitEvent(a.comp[0], a.small, 0));
   B200_TRY(cudaStreamWaitEvent(a.comp[1], a.small, 0));
@@ -246,12 +281,12 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
   int copied = 0, rc_run = B200ICP_OK;
   for (int c = 0; c < n_chunks; ++c) {
     if (need[c] > copied) {
-      if (run_dim == dim) {
-        B200_TRY(cudaMemcpyAsync(d + o_scans + (size_t)copied * row_bytes, scans + (size_t)copied * n_max * dim,
+      if (run_dim == pool.dim) {
+        B200_TRY(cudaMemcpyAsync(d + o_scans + (size_t)copied * row_bytes, scans + (size_t)copied * pool.n_max * pool.dim,
                                  (size_t)(need[c] - copied) * row_bytes, cudaMemcpyHostToDevice, a.copy));
       } else {   // (x, y) rows into (x, y, 0) rows
-        B200_TRY(cudaMemcpy2DAsync(d + o_scans + (size_t)copied * row_bytes, 24, scans + (size_t)copied * n_max * 2, 16,
-                                   16, (size_t)(need[c] - copied) * n_max, cudaMemcpyHostToDevice, a.copy));
+        B200_TRY(cudaMemcpy2DAsync(d + o_scans + (size_t)copied * row_bytes, 24, scans + (size_t)copied * pool.n_max * 2, 16,
+                                   16, (size_t)(need[c] - copied) * pool.n_max, cudaMemcpyHostToDevice, a.copy));
       }
       copied = need[c];
     }
@@ -261,31 +296,101 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
     cudaStream_t st = a.comp[c & 1];
     B200_TRY(cudaStreamWaitEvent(st, a.ready[c], 0));
     const size_t b0 = (size_t)lo[c];
-    rc_run = b200icp_run(reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts),
-                         n_scans, n_max, run_dim, reinterpret_cast<const int32_t*>(d + o_pairs) + 2 * b0,
-                         reinterpret_cast<const double*>(d + o_init) + 16 * b0,
-                         reinterpret_cast<const double*>(d + o_eps) + b0,
-                         reinterpret_cast<const uint8_t*>(d + o_norm) + b0, nb, max_iters, stopping_thresh,
-                         reinterpret_cast<double*>(d + o_T) + 16 * b0, reinterpret_cast<double*>(d + o_err) + b0,
-                         reinterpret_cast<int32_t*>(d + o_iters) + b0, reinterpret_cast<int32_t*>(d + o_status) + b0,
-                         corr_out ? reinterpret_cast<int32_t*>(d + o_corr) + b0 * n_max : nullptr,
-                         d + o_ws[c], ws_bytes[c], st);
+    rc_run = b200icp_run_ex(reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts),
+                            pool.n_scans, pool.n_max, run_dim, reinterpret_cast<const int32_t*>(d + o.pairs) + 2 * b0,
+                            reinterpret_cast<const double*>(d + o.init) + 16 * b0,
+                            reinterpret_cast<const double*>(d + o.eps) + b0,
+                            reinterpret_cast<const uint8_t*>(d + o.norm) + b0, nb, io.max_iters, io.stopping_thresh,
+                            reinterpret_cast<double*>(d + o.T) + 16 * b0, reinterpret_cast<double*>(d + o.err) + b0,
+                            reinterpret_cast<int32_t*>(d + o.iters) + b0, reinterpret_cast<int32_t*>(d + o.status) + b0,
+                            io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) + b0 * pool.n_max : nullptr,
+                            d + o_ws[c], ws_bytes[c], st, nullptr, io.peers, io.n_peers, io.peer_row0 + (long long)b0,
+                            io.flags);
     if (rc_run != B200ICP_OK) break;
   }
-  // results back once both compute streams are done
-  for (int k = 0; k < 2; ++k) {
+  for (int k = 0; k < 2; ++k) {   // results back once both compute streams are done
     B200_TRY(cudaEventRecord(a.done[k], a.comp[k]));
     B200_TRY(cudaStreamWaitEvent(a.copy, a.done[k], 0));
   }
   if (rc_run == B200ICP_OK) {
-    B200_TRY(cudaMemcpyAsync(T_out, d + o_T, (size_t)n_pairs * 128, cudaMemcpyDeviceToHost, a.copy));
-    if (err_out) B200_TRY(cudaMemcpyAsync(err_out, d + o_err, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, a.copy));
-    if (iters_out) B200_TRY(cudaMemcpyAsync(iters_out, d + o_iters, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
-    if (status_out) B200_TRY(cudaMemcpyAsync(status_out, d + o_status, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, a.copy));
-    if (corr_out) B200_TRY(cudaMemcpyAsync(corr_out, d + o_corr, (size_t)n_pairs * n_max * 4, cudaMemcpyDeviceToHost, a.copy));
+    const int rc_dn = download_results(a, d, o, io, pool.n_max);
+    if (rc_dn != B200ICP_OK) return rc_dn;
   }
   B200_TRY(cudaStreamSynchronize(a.copy));
   return rc_run;
+}
+
+int run_host_impl(const HostPool& pool, HostIo io) {
+  if (!pool.data || !io.pairs || !io.init || !io.epsilon || !io.normalize || !io.T_out || pool.n_scans <= 0 ||
+      pool.n_max <= 0 || io.n_pairs < 0 || io.max_iters < 0 || (pool.dim != 2 && pool.dim != 3) ||
+      ((size_t)pool.n_max * pool.dim) % 2 != 0)
+    return B200ICP_ERR_BAD_ARG;
+  if (io.n_peers < 0 || io.n_peers > 16 || (io.n_peers > 0 && !io.peers) || io.peer_row0 < 0) return B200ICP_ERR_BAD_ARG;
+  if (io.n_pairs == 0) return B200ICP_OK;
+  io.flags |= b200icp::env_flags();
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return B200ICP_ERR_NO_DEVICE; }
+  std::lock_guard<std::mutex> lock(g_mutex);
+  HostArena& a = g_arena[dev];
+  if (!arena_init(a)) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
+
+  if (pool.kind != 0) return run_gated(a, pool, io);   // ranges: always the planar kernel, one launch
+
+  // An initial transform that leaves the plane: the reference lifts the scans to z = 0 and carries
+  // on in 3-D (icp.py:153-156), so the whole batch goes through the general kernel on a z-padded pool.
+  int run_dim = pool.dim;
+  if (pool.dim == 2)
+    for (int b = 0; b < io.n_pairs; ++b)
+      if (!keeps_plane(io.init + (size_t)b * 16)) { run_dim = 3; break; }
+  const bool gated = run_dim == 2 && pool.n_max <= kMax2dPoints && io.n_pairs >= kPipelineMinPairs &&
+                     !(io.flags & B200ICP_FLAG_HOST_CHUNKED);
+  return gated ? run_gated(a, pool, io) : run_chunked(a, pool, io, run_dim);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200icp_run_host_ex(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                        const int32_t* pairs, const double* init, const double* epsilon,
+                        const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                        double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                        int32_t* corr_out, double* const* peer_pose_out, int n_peers, long long peer_row0,
+                        unsigned flags) {
+  if (!counts) return B200ICP_ERR_BAD_ARG;
+  HostPool pool{};
+  pool.data = scans; pool.kind = 0; pool.n_scans = n_scans; pool.n_max = n_max; pool.dim = dim; pool.counts = counts;
+  HostIo io{pairs, init, epsilon, normalize, n_pairs, max_iters, stopping_thresh, T_out, err_out, iters_out,
+            status_out, corr_out, peer_pose_out, n_peers, peer_row0, flags};
+  return run_host_impl(pool, io);
+}
+
+int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                     const int32_t* pairs, const double* init, const double* epsilon,
+                     const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                     double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                     int32_t* corr_out) {
+  return b200icp_run_host_ex(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
+                             stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, nullptr, 0, 0, 0u);
+}
+
+int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
+                            const double* sin_tab, double range_min, double range_max, double off_x, double off_y,
+                            const int32_t* pairs, const double* init, const double* epsilon,
+                            const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                            double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                            int32_t* corr_out, int32_t* counts_out, double* const* peer_pose_out, int n_peers,
+                            long long peer_row0, unsigned flags) {
+  if (!cos_tab || !sin_tab || n_beams <= 0 || n_beams > kMax2dPoints || (ranges_dtype != 0 && ranges_dtype != 1))
+    return B200ICP_ERR_BAD_ARG;
+  HostPool pool{};
+  pool.data = ranges; pool.kind = ranges_dtype ? 2 : 1; pool.n_scans = n_scans; pool.n_beams = n_beams;
+  pool.n_max = n_beams + (n_beams & 1); pool.dim = 2;
+  pool.cos_tab = cos_tab; pool.sin_tab = sin_tab; pool.range_min = range_min; pool.range_max = range_max;
+  pool.off_x = off_x; pool.off_y = off_y; pool.counts_out = counts_out;
+  HostIo io{pairs, init, epsilon, normalize, n_pairs, max_iters, stopping_thresh, T_out, err_out, iters_out,
+            status_out, corr_out, peer_pose_out, n_peers, peer_row0, flags};
+  return run_host_impl(pool, io);
 }
 
 int b200icp_host_release(void) {

@@ -278,9 +278,36 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
   for (;;) {
     __syncthreads();  // previous pair fully consumed; mbarrier initialised
     PHASE(7);
-    if (tid == 0) *s_pair = (int)atomicAdd(p.queue, 1u);
+    if (tid == 0) {
+      const int pr = (int)atomicAdd(p.queue, 1u);
+      s_pair[0] = pr;
+      int resident = 1;
+      if (p.ready_scans && pr < p.n_pairs) {
+        // Gated launch: wait until the copy stream has delivered both scans of this pair.  Bounded:
+        // a caller whose copies never arrive must not hang the device.  After 5 s the pair is given
+        // up (status NOT_RESIDENT, it is not staged), queue[5] tells the host side, and from then on
+        // nobody waits: pairs whose scans are still missing are given up at once.
+        const int a = p.pairs[2 * pr], b = p.pairs[2 * pr + 1];
+        if (a >= 0 && b >= 0 && a < p.n_scans && b < p.n_scans) {
+          const unsigned need = (unsigned)max(a, b) + 1u;
+          if (ld_acquire_sys(p.ready_scans) < need) {
+            volatile unsigned* gave_up = p.queue + 5;
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while (ld_acquire_sys(p.ready_scans) < need && *gave_up == 0u) {
+              __nanosleep(500);
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+              if (t1 - t0 > p.gate_timeout_ns) *gave_up = 1u;
+            }
+            resident = ld_acquire_sys(p.ready_scans) >= need ? 1 : 0;
+          }
+          fence_proxy_async_global();
+        }
+      }
+      s_pair[1] = resident;
+    }
     __syncthreads();
-    const int pair = *s_pair;
+    const int pair = s_pair[0];
     if (pair >= p.n_pairs) break;
 
     const int si = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
@@ -288,6 +315,8 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     int ns = 0, nt = 0;
     if (si < 0 || ti < 0 || si >= p.n_scans || ti >= p.n_scans) {
       early = B200ICP_STATUS_SKIPPED;
+    } else if (!s_pair[1]) {
+      early = B200ICP_STATUS_NOT_RESIDENT;
     } else {
       ns = min(p.counts[si], p.n_max);
       nt = min(p.counts[ti], p.n_max);
@@ -324,23 +353,6 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
 
     // ---- stage both scans with TMA bulk copies --------------------------------
     if (tid == 0) {
-      if (p.ready_scans) {   // gated launch: wait until the copy stream has delivered both scans
-        const unsigned need = (unsigned)max(si, ti) + 1u;
-        // Bounded (last resort): a caller whose copies never arrive must not hang the device.  A
-        // wait of more than 5 s gives up, and from then on nobody waits; queue[5] tells the host
-        // side that the results are void.
-        if (ld_acquire_sys(p.ready_scans) < need) {
-          volatile unsigned* gave_up = p.queue + 5;
-          unsigned long long t0, t1;
-          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-          while (ld_acquire_sys(p.ready_scans) < need && *gave_up == 0u) {
-            __nanosleep(500);
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > 5000000000ull) *gave_up = 1u;
-          }
-        }
-        fence_proxy_async_global();
-      }
       fence_proxy_async();
       mbar_expect_tx(mbar, (uint32_t)(ns + nt) * 16u);
       tma_load_1d(s64, p.scans + (size_t)si * p.n_max * 2, (uint32_t)ns * 16u, mbar);

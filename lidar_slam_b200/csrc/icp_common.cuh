@@ -7,6 +7,8 @@
 
 namespace b200icp {
 
+unsigned env_flags();   // developer overrides from the environment, read once (api.cu)
+
 constexpr int kBlockTargets = 32;          // targets per bookkeeping block in the NN sweep
 constexpr float kU = 5.9604644775390625e-8f;  // 2^-24, fp32 unit round-off
 constexpr float kBigCoord = 1.0e18f;       // sentinel coordinate for padded targets
@@ -77,7 +79,8 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
 // factor 2 to spare.  A candidate set {t : d32(t) <= m + 2*slack} around the
 // fp32 minimum m therefore always contains the float64 nearest neighbour; the
 // callers use 4*slack (and evaluate at an upper bound of m).
-// tests/test_margin.py checks the inequality on adversarial inputs.
+// tests/test_host.py::test_fp32_slack_bounds_the_float64_distance checks the inequality on adversarial inputs
+// (tests/test_margin.py adds near-ties, large offsets and denormals).
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ float slack(float d_hi, float a_bound) {
   float s = sqrtf(d_hi);
@@ -236,6 +239,15 @@ struct RunParams {
   // gated launch (b200icp_run_gated): scans [0, *ready_scans) of the pool are resident; the value
   // is raised by copies on another stream while the kernel runs.  Null: the whole pool is resident.
   const unsigned int* ready_scans;
+  unsigned long long gate_timeout_ns;   // gated launch: give a pair up after waiting this long for its scans
+  // RANGES mode (b200icp_run_ranges): the pool is [n_scans, n_beams] ranges (float64, or float32 when
+  // ranges_f32), scans == counts == nullptr; the planar kernel builds the two scans of a pair itself.
+  const void* ranges;
+  int ranges_f32, n_beams;
+  const double* cos_tab;
+  const double* sin_tab;
+  double range_min, range_max, off_x, off_y;
+  int32_t* counts_out;                  // [n_scans] or nullptr: valid beams per scan
 };
 
 // kept out of line: atan2's slow path must not widen the register footprint of the ICP loops

@@ -19,8 +19,9 @@ from . import _lib
 
 STATUS_NAMES = {
     0: "epsilon", 1: "max_iters", 2: "stalled", 3: "nonfinite", 4: "empty", 5: "nonplanar_init",
-    6: "skipped",
+    6: "skipped", 7: "not_resident",
 }
+FLAG_EXHAUSTIVE, FLAG_HOST_CHUNKED, FLAG_NO_PRUNE = _lib.FLAG_EXHAUSTIVE, _lib.FLAG_HOST_CHUNKED, _lib.FLAG_NO_PRUNE
 STATUS_NONPLANAR = 5
 
 
@@ -100,7 +101,7 @@ def _per_pair(x, n, dtype, dev):
 
 
 _PIPELINE_MIN_PAIRS = 2048
-_PIPELINE_CHUNKS = int(os.environ.get("B200ICP_PIPELINE_CHUNKS", "6"))
+_PIPELINE_CHUNKS = 6
 _SIDE_STREAMS = {}
 
 
@@ -186,7 +187,7 @@ def _copy_pool_pipelined(host_pool, dev_pool, pairs_host, dev, launch_chunk):
 
 def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_iters=2000,
                   stopping_thresh=0.0001, normalize_error=False, return_correspondences=False,
-                  planar_fallback=True, peer_pose_ptrs=None, peer_row0=0) -> IcpBatchResult:
+                  planar_fallback=True, peer_pose_ptrs=None, peer_row0=0, flags=0) -> IcpBatchResult:
     """Align every (source, target) pair of `pairs` in one launch.
 
     scans  [S, n_max, D] float64 (D = 2 or 3), counts [S] int32 (see pack_scans);
@@ -198,6 +199,12 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     peer_pose_ptrs: optional list of peer-mapped device pointers (one gather buffer per rank);
     the kernel then also stores every pair's (x, y, theta, error) row into row peer_row0 + b of
     each buffer (b200icp_run_exchange; see run_icp_sharded).
+    flags: B200ICP_FLAG_* (FLAG_EXHAUSTIVE, FLAG_NO_PRUNE: same results, for A/B timing and tests).
+
+    Asynchronous on the current stream, with one exception: a big batch whose scan pool is a PINNED
+    HOST tensor is streamed to the device under a gated launch, and that path synchronises before it
+    returns (it must check that the kernel never gave up waiting for a slice), so the host pool may
+    be refilled as soon as the call returns.
     """
     lib = _lib.load()
     dev = scans.device if isinstance(scans, torch.Tensor) and scans.is_cuda else _device()
@@ -255,36 +262,28 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     global _last_workspace
     _last_workspace = ws
 
-    def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax, ws=ws, row0=0):
+    def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax, ws=ws, row0=0, gate=None):
+        peers, n_peers = None, 0
+        if peer_pose_ptrs:
+            peers_arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
+            peers, n_peers = ctypes.cast(peers_arr, ctypes.c_void_p), len(peer_pose_ptrs)
         with torch.cuda.device(dev):
-            if peer_pose_ptrs:
-                peers = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
-                _lib.check(lib.b200icp_run_exchange(
-                    _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
-                    _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
-                    _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
-                    _stream_ptr(), ctypes.cast(peers, ctypes.c_void_p), len(peer_pose_ptrs), int(peer_row0) + row0),
-                    "b200icp_run_exchange")
-                return
-            _lib.check(lib.b200icp_run(
+            _lib.check(lib.b200icp_run_ex(
                 _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
                 _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
                 _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
-                _stream_ptr()), "b200icp_run")
+                _stream_ptr(), _ptr(gate), peers, n_peers, int(peer_row0) + row0, int(flags)), "b200icp_run_ex")
 
     if host_pool is not None and dim == 2 and n_max <= 2048 and (planar_ok or not planar_fallback):
-        def launch_gated(flag):
-            peers, n_peers = None, 0
-            if peer_pose_ptrs:
-                peers_arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
-                peers, n_peers = ctypes.cast(peers_arr, ctypes.c_void_p), len(peer_pose_ptrs)
-            with torch.cuda.device(dev):
-                _lib.check(lib.b200icp_run_gated(
-                    _ptr(scans), _ptr(counts), n_scans, n_max, dim, _ptr(pairs), _ptr(init), _ptr(eps), _ptr(norm),
-                    n_pairs, int(max_iters), float(stopping_thresh), _ptr(T), _ptr(err), _ptr(iters), _ptr(status),
-                    _ptr(corr), _ptr(ws), ws.numel(), _stream_ptr(), _ptr(flag), peers, n_peers, int(peer_row0)),
-                    "b200icp_run_gated")
-        _copy_pool_gated(host_pool, scans, dev, launch_gated)
+        _copy_pool_gated(host_pool, scans, dev,
+                         lambda flag: launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max,
+                                             gate=flag))
+        # the gated kernel gives a pair up (status 7) rather than hang if its scans never arrive:
+        # that must not pass for a result (workspace word 5, include/b200icp.h)
+        torch.cuda.current_stream(dev).synchronize()
+        if int(ws[20:24].cpu().numpy().view(np.uint32)[0]) != 0:
+            raise RuntimeError("b200icp_run_gated: the scan pool did not arrive within the wait limit; "
+                               "pairs with status 7 (not_resident) were not aligned")
         return IcpBatchResult(T, err, iters, status, corr)
     if host_pool is not None:
         _copy_pool_pipelined(host_pool, scans, pairs_host, dev,
@@ -306,6 +305,66 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     else:
         launch(dim, scans, pairs, init, eps, norm, T, err, iters, status, corr, n_max)
     return IcpBatchResult(T, err, iters, status, corr)
+
+
+def run_icp_ranges_batch(ranges, pairs, init_transforms=None, epsilon=0.01, max_iters=2000, stopping_thresh=0.0001,
+                         normalize_error=False, return_correspondences=False, range_min=0.1, range_max=30.0,
+                         offset_xy=(0.13323, 0.0), peer_pose_ptrs=None, peer_row0=0, flags=0):
+    """run_icp_batch over a pool of lidar RANGES [S, n_beams] (float64, or float32 when every range is
+    float32-representable) instead of points: get_lidar_data (modules/localization.py:252-307) is
+    fused into the planar kernel's staging (b200icp_run_ranges), bit-identical to
+    scans.scans_from_ranges + run_icp_batch.  Returns (IcpBatchResult, counts [S] int32: valid beams of
+    every scan a pair referenced, -1 elsewhere).  Initial transforms must keep the plane."""
+    from .scans import beam_tables
+    lib = _lib.load()
+    dev = ranges.device if isinstance(ranges, torch.Tensor) and ranges.is_cuda else _device()
+    if isinstance(ranges, torch.Tensor) and ranges.dtype == torch.float32:
+        r = ranges.to(dev).contiguous()
+    elif isinstance(ranges, np.ndarray) and ranges.dtype == np.float32:
+        r = torch.from_numpy(np.ascontiguousarray(ranges)).to(dev)
+    else:
+        r = _to_dev(ranges, torch.float64, dev)
+    if r.dim() != 2 or r.shape[1] == 0 or r.shape[1] > 2048:
+        raise ValueError("ranges must have shape [S, n_beams] with n_beams <= 2048")
+    n_scans, n_beams = r.shape
+    n_max = n_beams + (n_beams & 1)
+    c, s_ = beam_tables(n_beams)
+    tab = torch.as_tensor(np.stack([c, s_])).to(dev)
+    pairs = _to_dev(pairs, torch.int32, dev).reshape(-1, 2)
+    n_pairs = pairs.shape[0]
+    if init_transforms is None:
+        init = torch.eye(4, dtype=torch.float64, device=dev).repeat(n_pairs, 1, 1)
+    else:
+        init = _to_dev(init_transforms, torch.float64, dev).reshape(-1, 4, 4)
+        if init.shape[0] != n_pairs:
+            raise ValueError("init_transforms must have one 4x4 per pair")
+    eps = _per_pair(epsilon, n_pairs, torch.float64, dev)
+    norm = _per_pair(normalize_error, n_pairs, torch.uint8, dev)
+    T = torch.empty((n_pairs, 4, 4), dtype=torch.float64, device=dev)
+    err = torch.empty((n_pairs,), dtype=torch.float64, device=dev)
+    iters = torch.empty((n_pairs,), dtype=torch.int32, device=dev)
+    status = torch.empty((n_pairs,), dtype=torch.int32, device=dev)
+    corr = torch.empty((n_pairs, n_max), dtype=torch.int32, device=dev) if return_correspondences else None
+    counts = torch.full((n_scans,), -1, dtype=torch.int32, device=dev)
+    if n_pairs == 0:
+        return IcpBatchResult(T, err, iters, status, corr), counts
+    nbytes = ctypes.c_size_t()
+    _lib.check(lib.b200icp_workspace_bytes(n_pairs, n_max, 2, ctypes.byref(nbytes)), "b200icp_workspace_bytes")
+    ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
+    global _last_workspace
+    _last_workspace = ws
+    peers, n_peers = None, 0
+    if peer_pose_ptrs:
+        peers_arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
+        peers, n_peers = ctypes.cast(peers_arr, ctypes.c_void_p), len(peer_pose_ptrs)
+    with torch.cuda.device(dev):
+        _lib.check(lib.b200icp_run_ranges(
+            _ptr(r), 1 if r.dtype == torch.float32 else 0, n_scans, n_beams, _ptr(tab[0]), _ptr(tab[1]),
+            float(range_min), float(range_max), float(offset_xy[0]), float(offset_xy[1]), _ptr(pairs), _ptr(init),
+            _ptr(eps), _ptr(norm), n_pairs, int(max_iters), float(stopping_thresh), _ptr(T), _ptr(err), _ptr(iters),
+            _ptr(status), _ptr(corr), _ptr(counts), _ptr(ws), ws.numel(), _stream_ptr(), None, peers, n_peers,
+            int(peer_row0), int(flags)), "b200icp_run_ranges")
+    return IcpBatchResult(T, err, iters, status, corr), counts
 
 
 _last_workspace = None

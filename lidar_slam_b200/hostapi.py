@@ -56,11 +56,21 @@ def _p(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 
 
+def _peer_array(peer_pose_ptrs):
+    if not peer_pose_ptrs:
+        return None, 0
+    arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
+    return arr, len(peer_pose_ptrs)
+
+
 def run_icp_batch_host(scans: np.ndarray, counts: np.ndarray, pairs: np.ndarray, init_transforms=None,
                        epsilon=0.01, max_iters: int = 2000, stopping_thresh: float = 1e-4,
-                       normalize_error=False, return_correspondences: bool = False) -> HostBatchResult:
+                       normalize_error=False, return_correspondences: bool = False, flags: int = 0,
+                       peer_pose_ptrs=None, peer_row0: int = 0) -> HostBatchResult:
     """run_icp (modules/icp.py:123-189) for every (source, target) row of `pairs` over a padded scan
-    pool in host memory; same per-pair semantics and defaults as the reference call."""
+    pool in host memory; same per-pair semantics and defaults as the reference call.
+    flags: B200ICP_FLAG_* (_lib.FLAG_*); peer_pose_ptrs / peer_row0: the fused multi-GPU pose exchange
+    (device pointers of every rank's gather buffer, include/b200icp.h)."""
     lib = _lib.load()
     scans = np.ascontiguousarray(scans, dtype=np.float64)
     if scans.ndim != 3 or scans.shape[2] not in (2, 3):
@@ -86,10 +96,74 @@ def run_icp_batch_host(scans: np.ndarray, counts: np.ndarray, pairs: np.ndarray,
     iters = np.empty((n_pairs,), dtype=np.int32)
     status = np.empty((n_pairs,), dtype=np.int32)
     corr = np.empty((n_pairs, n_max), dtype=np.int32) if return_correspondences else None
-    _lib.check(lib.b200icp_run_host(_p(scans), _p(counts), n_scans, n_max, dim, _p(pairs), _p(init), _p(eps),
-                                    _p(norm), n_pairs, int(max_iters), float(stopping_thresh), _p(T), _p(err),
-                                    _p(iters), _p(status), _p(corr)), "b200icp_run_host")
+    peers, n_peers = _peer_array(peer_pose_ptrs)
+    _lib.check(lib.b200icp_run_host_ex(_p(scans), _p(counts), n_scans, n_max, dim, _p(pairs), _p(init), _p(eps),
+                                       _p(norm), n_pairs, int(max_iters), float(stopping_thresh), _p(T), _p(err),
+                                       _p(iters), _p(status), _p(corr),
+                                       None if peers is None else ctypes.cast(peers, ctypes.c_void_p), n_peers,
+                                       int(peer_row0), int(flags)), "b200icp_run_host_ex")
     return HostBatchResult(T, err, iters, status, corr)
+
+
+def beam_tables(n_beams: int):
+    """cos / sin of linspace(-135 deg, +135 deg, n_beams) exactly as the reference evaluates them
+    (modules/localization.py:273-278), numpy on the host."""
+    angles = np.linspace(-135 * (np.pi / 180), 135 * (np.pi / 180), n_beams)
+    return np.cos(angles), np.sin(angles)
+
+
+class HostRangesWorkspace:
+    """Reusable host-side buffers for run_icp_ranges_host (results land in the same arrays on every
+    call, so that a caller who loops pays no allocation; pass `out=` to reuse)."""
+
+    def __init__(self, n_pairs: int, n_scans: int, n_max: int, correspondences: bool = False):
+        self.T = np.empty((n_pairs, 4, 4), dtype=np.float64)
+        self.err = np.empty((n_pairs,), dtype=np.float64)
+        self.iters = np.empty((n_pairs,), dtype=np.int32)
+        self.status = np.empty((n_pairs,), dtype=np.int32)
+        self.corr = np.empty((n_pairs, n_max), dtype=np.int32) if correspondences else None
+        self.counts = np.empty((n_scans,), dtype=np.int32)
+
+
+def run_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms=None, epsilon=0.01,
+                        max_iters: int = 2000, stopping_thresh: float = 1e-4, normalize_error=False,
+                        return_correspondences: bool = False, range_min: float = 0.1, range_max: float = 30.0,
+                        offset_xy=(0.13323, 0.0), flags: int = 0, peer_pose_ptrs=None, peer_row0: int = 0,
+                        out: Optional[HostRangesWorkspace] = None, tables=None):
+    """get_lidar_data (modules/localization.py:252-307) + run_icp (modules/icp.py:123-189) for every
+    (source, target) row of `pairs`, from the synced lidar ranges [S, n_beams] in host memory (float64
+    as the reference holds them, or a float32 copy): b200icp_run_host_ranges.  Returns
+    (HostBatchResult, counts [S] int32)."""
+    lib = _lib.load()
+    if ranges.dtype not in (np.float64, np.float32):
+        ranges = np.asarray(ranges, dtype=np.float64)
+    ranges = np.ascontiguousarray(ranges)
+    if ranges.ndim != 2 or ranges.shape[1] == 0 or ranges.shape[1] > 2048:
+        raise ValueError("ranges must be [S, n_beams] with n_beams <= 2048")
+    n_scans, n_beams = ranges.shape
+    n_max = n_beams + (n_beams & 1)
+    cos_t, sin_t = tables if tables is not None else beam_tables(n_beams)
+    cos_t, sin_t = np.ascontiguousarray(cos_t, dtype=np.float64), np.ascontiguousarray(sin_t, dtype=np.float64)
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    n_pairs = pairs.shape[0]
+    if init_transforms is None:
+        init = np.broadcast_to(np.eye(4), (n_pairs, 4, 4)).copy()
+    else:
+        init = np.ascontiguousarray(init_transforms, dtype=np.float64).reshape(-1, 4, 4)
+        if init.shape[0] != n_pairs:
+            raise ValueError("init_transforms must have one 4x4 per pair")
+    eps = _per_pair(epsilon, n_pairs, np.float64)
+    norm = _per_pair(normalize_error, n_pairs, np.uint8)
+    o = out if out is not None else HostRangesWorkspace(n_pairs, n_scans, n_max, return_correspondences)
+    peers, n_peers = _peer_array(peer_pose_ptrs)
+    _lib.check(lib.b200icp_run_host_ranges(
+        _p(ranges), 1 if ranges.dtype == np.float32 else 0, n_scans, n_beams, _p(cos_t), _p(sin_t), float(range_min),
+        float(range_max), float(offset_xy[0]), float(offset_xy[1]), _p(pairs), _p(init), _p(eps), _p(norm), n_pairs,
+        int(max_iters), float(stopping_thresh), _p(o.T), _p(o.err), _p(o.iters), _p(o.status),
+        _p(o.corr) if return_correspondences else None, _p(o.counts),
+        None if peers is None else ctypes.cast(peers, ctypes.c_void_p), n_peers, int(peer_row0), int(flags)),
+        "b200icp_run_host_ranges")
+    return HostBatchResult(o.T, o.err, o.iters, o.status, o.corr if return_correspondences else None), o.counts
 
 
 def release() -> None:

@@ -73,12 +73,15 @@ def make_trajectories(n_traj, n_steps, seed):
 
 
 def cast_scans(poses, seed, device="cpu", chunk=2048, noise_sigma=0.01,
-               invalid_frac=0.005):
+               invalid_frac=0.005, return_ranges=False):
     """Ray-cast one scan per pose.
 
     poses: (S,3) array-like of robot poses (x, y, theta) in the world.
     Returns (scans[S,1081,2] float64, counts[S] int32) on `device`; the valid
     points of each scan are packed to the front in beam order, the tail is 0.
+    return_ranges: also return the measured ranges [S,1081] float64 (what the
+    reference's Hokuyo log holds: millimetre-quantised, float32-representable,
+    dropped beams 0), the input of get_lidar_data (localization.py:252-307).
     """
     poses = torch.as_tensor(np.asarray(poses), dtype=torch.float64)
     n_scans = poses.shape[0]
@@ -89,6 +92,7 @@ def cast_scans(poses, seed, device="cpu", chunk=2048, noise_sigma=0.01,
     beam = torch.linspace(ANGLE_MIN, ANGLE_MAX, N_BEAMS, dtype=torch.float64, device=device)
     scans = torch.zeros((n_scans, N_BEAMS, 2), dtype=torch.float64, device=device)
     counts = torch.zeros((n_scans,), dtype=torch.int32, device=device)
+    ranges = torch.zeros((n_scans, N_BEAMS), dtype=torch.float64, device=device) if return_ranges else None
     for lo in range(0, n_scans, chunk):
         p = poses[lo:lo + chunk].to(device)
         m = p.shape[0]
@@ -110,6 +114,8 @@ def cast_scans(poses, seed, device="cpu", chunk=2048, noise_sigma=0.01,
         meas = rng_true + noise_sigma * noise
         meas = (torch.round(meas * 1000.0) / 1000.0).to(torch.float32).to(torch.float64)
         meas = torch.where(drop, torch.zeros_like(meas), meas)
+        if ranges is not None:
+            ranges[lo:lo + m] = meas
         valid = (meas >= RANGE_MIN) & (meas <= RANGE_MAX)
         px = meas * torch.cos(beam)[None, :] + LIDAR_FORWARD
         py = meas * torch.sin(beam)[None, :]
@@ -121,6 +127,8 @@ def cast_scans(poses, seed, device="cpu", chunk=2048, noise_sigma=0.01,
         scans[lo:lo + m, :, 0] = torch.where(keep, px, torch.zeros_like(px))
         scans[lo:lo + m, :, 1] = torch.where(keep, py, torch.zeros_like(py))
         counts[lo:lo + m] = n_valid.to(torch.int32)
+    if return_ranges:
+        return scans, counts, ranges
     return scans, counts
 
 
@@ -158,28 +166,33 @@ def perturb_planar(transforms, seed, sigma_t=0.01, sigma_r=0.003):
     return out
 
 
-def odometry_batch(n_pairs, seed=20, device="cpu", n_traj=None):
+def odometry_batch(n_pairs, seed=20, device="cpu", n_traj=None, with_ranges=False):
     """Config-2 / config-5 shaped workload.
 
     Returns dict(scans[S,1081,2], counts[S], pairs[B,2] (src,tgt), init[B,4,4]).
     Pair i aligns scan i+1 (source) to scan i (target) inside one trajectory,
     initialised with perturbed true motion, like localization.py:112-123.
+    with_ranges: also "ranges" [S,1081] float64, the lidar log the scans come from.
     """
     if n_traj is None:
         n_traj = max(1, n_pairs // 4955)
     per = -(-n_pairs // n_traj)            # pairs per trajectory
     poses = make_trajectories(n_traj, per + 1, seed)
-    scans, counts = cast_scans(poses.reshape(-1, 3), seed + 1, device=device)
+    cast = cast_scans(poses.reshape(-1, 3), seed + 1, device=device, return_ranges=with_ranges)
+    scans, counts = cast[0], cast[1]
     src = (np.arange(n_traj)[:, None] * (per + 1) + np.arange(1, per + 1)[None, :]).reshape(-1)
     pairs = np.stack([src, src - 1], axis=1)[:n_pairs].astype(np.int32)
     init = np.concatenate([relative_motions(poses[t]) for t in range(n_traj)], axis=0)[:n_pairs]
     init = perturb_planar(init, seed + 2)
-    return {
+    out = {
         "scans": scans, "counts": counts,
         "pairs": torch.as_tensor(pairs, device=device),
         "init": torch.as_tensor(init, device=device),
         "poses": poses,
     }
+    if with_ranges:
+        out["ranges"] = cast[2]
+    return out
 
 
 def thin_scans(scans, counts, seed, lo=100, hi=N_BEAMS):

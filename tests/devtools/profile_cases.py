@@ -24,8 +24,8 @@ elif case == "texture":
     for _ in range(2):
         p.paint_frames(d, c, x_ts)
     p.resolve(None)
-elif case == "icp3d":
-    src = synth.drill_cloud(6000, seed=1)
+elif case in ("icp3d", "icp3d_20k"):
+    src = synth.drill_cloud(20000 if case == "icp3d_20k" else 6000, seed=1)
     tgts = [synth.partial_view(src, seed=10 + k) for k in range(4)]
     pool, counts = eng.pack_scans([src] + tgts)
     pairs, inits = [], []

@@ -38,7 +38,7 @@ def test_host_entry_equals_oracle_small_batch():
 def test_pipelined_host_entry_equals_device_entry_bitwise():
     """3000 consecutive pairs: ONE gated launch while the pool arrives in slices (the kernel waits
     per pair on the device-side counter of resident scans); the same pairs in shuffled order (the
-    first pairs then wait for most of the pool); and the chunked path (B200ICP_HOST_GATED=0: six
+    first pairs then wait for most of the pool); and the chunked path (FLAG_HOST_CHUNKED: six
     launches over two streams) that the general kernel still uses."""
     import torch
     import lidar_slam_b200 as eng
@@ -56,19 +56,13 @@ def test_pipelined_host_entry_equals_device_entry_bitwise():
     assert np.array_equal(shuf.T, host.T[perm]) and np.array_equal(shuf.iters, host.iters[perm])
     again = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
     assert np.array_equal(again.T, host.T)          # arena reuse
-    import os
-    os.environ["B200ICP_HOST_GATED"] = "0"
-    try:
-        chunked = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
-    finally:
-        del os.environ["B200ICP_HOST_GATED"]
+    from lidar_slam_b200 import _lib
+    chunked = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3,
+                                         flags=_lib.FLAG_HOST_CHUNKED)
     assert np.array_equal(chunked.T, host.T) and np.array_equal(chunked.iters, host.iters)
-    for slices in ("1", "3", "63", "1000"):
-        os.environ["B200ICP_HOST_SLICES"] = slices
-        try:
-            r = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
-        finally:
-            del os.environ["B200ICP_HOST_SLICES"]
+    for slices in (1, 3, 63, 200):
+        r = hostapi.run_icp_batch_host(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3,
+                                       flags=_lib.flag_slices(slices))
         assert np.array_equal(r.T, host.T) and np.array_equal(r.error, host.error), slices
 
 

@@ -1,10 +1,12 @@
 """The block-pruned NN sweep of the planar kernel against its exhaustive variant and the oracle.
 
-The shipped kernel skips target blocks whose bounding-box lower bound exceeds the candidate
-threshold (icp2d.cuh); `B200ICP_SWEEP=exhaustive` (read at every launch) evaluates every
-candidate.  Both must give the SAME bits -- poses, errors, pass counts, correspondences -- on
-every input, including inputs on which pruning has nothing to prune (shuffled clouds) and the
-degenerate block counts.  The oracle check (exhaustive float64 search) closes the triangle.
+The shipped kernel (icp2d_rows.cuh) skips target blocks whose bounding-box lower bound exceeds the
+candidate threshold; FLAG_NO_PRUNE sweeps every block in the same kernel and FLAG_EXHAUSTIVE runs the
+register-tiled exhaustive kernel of round 1 (icp2d.cuh).  Pruned and unpruned must give the SAME bits
+-- poses, errors, pass counts, correspondences -- on every input, including inputs on which pruning
+has nothing to prune (shuffled clouds) and the degenerate block counts; the exhaustive kernel sums in
+another order, so it must give the same matches, pass counts and statuses and poses equal to
+rounding.  The oracle check (exhaustive float64 search) closes the triangle.
 """
 import os
 
@@ -21,18 +23,24 @@ def _eng():
 
 
 def _both(fn):
-    """fn() under the pruned (default) and the exhaustive sweep."""
-    old = os.environ.pop("B200ICP_SWEEP", None)
-    try:
-        a = fn()
-        os.environ["B200ICP_SWEEP"] = "exhaustive"
-        b = fn()
-    finally:
-        os.environ.pop("B200ICP_SWEEP", None)
-        if old is not None:
-            os.environ["B200ICP_SWEEP"] = old
+    """fn(flags) under the shipped row kernel (pruned), the same kernel with the block bounds switched
+    off (FLAG_NO_PRUNE: every block swept, same summation order) and the exhaustive register-tiled
+    kernel of round 1 (FLAG_EXHAUSTIVE).  The first two must agree bit for bit; the third sums in
+    another order, so its matches / pass counts / statuses must be equal and its poses and errors
+    equal to rounding.  Returns (pruned, unpruned)."""
+    from lidar_slam_b200 import engine
+    a = fn(0)
+    b = fn(engine.FLAG_NO_PRUNE)
+    e = fn(engine.FLAG_EXHAUSTIVE)
+    for name in ("iters", "status", "corr"):
+        x, y = getattr(a, name), getattr(e, name)
+        if x is not None:
+            assert torch.equal(x, y), "exhaustive kernel: " + name
+    fin = torch.isfinite(a.error)
+    assert torch.equal(fin, torch.isfinite(e.error))
+    assert torch.allclose(a.T[fin], e.T[fin], rtol=1e-11, atol=1e-11)
+    assert torch.allclose(a.error[fin], e.error[fin], rtol=1e-11, atol=0)
     return a, b
-
 
 def _same(a, b):
     for name in ("T", "error", "iters", "status", "corr"):
@@ -47,19 +55,15 @@ def test_pruned_equals_exhaustive_on_lidar_batch():
     eng = _eng()
     from lidar_slam_b200 import engine, synth
     b = synth.odometry_batch(600, seed=3, device="cuda")
-    run = lambda: eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3,
-                                    return_correspondences=True)
+    run = lambda flags: eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3,
+                                          return_correspondences=True, flags=flags)
     a, e = _both(run)
     _same(a, e)
     # and pruning really happened on ordered scans (tile counter: workspace bytes 8..15)
     eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
     pruned_tiles = engine.swept_tiles()
-    os.environ["B200ICP_SWEEP"] = "exhaustive"
-    try:
-        eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
-        all_tiles = engine.swept_tiles()
-    finally:
-        del os.environ["B200ICP_SWEEP"]
+    eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, flags=engine.FLAG_NO_PRUNE)
+    all_tiles = engine.swept_tiles()
     assert 0 < pruned_tiles < 0.25 * all_tiles
 
 
@@ -80,8 +84,8 @@ def test_pruned_equals_exhaustive_and_oracle_on_shuffled_clouds(n_src, n_tgt):
     src = (tgt[pick] - np.array([0.03, -0.02])) @ Rm + rng.normal(scale=0.01, size=(n_src, 2))
     scans, counts = eng.pack_scans([src, tgt])
     pairs = np.array([[0, 1]], np.int32)
-    run = lambda: eng.run_icp_batch(scans, counts, pairs, None, epsilon=1e-6, max_iters=30,
-                                    return_correspondences=True)
+    run = lambda flags: eng.run_icp_batch(scans, counts, pairs, None, epsilon=1e-6, max_iters=30,
+                                          return_correspondences=True, flags=flags)
     a, e = _both(run)
     _same(a, e)
     T, err, corr, passes = orc.run_icp_info(src, tgt, np.eye(4), epsilon=1e-6, max_iters=30, nn="brute")
@@ -105,8 +109,8 @@ def test_pruned_equals_exhaustive_on_clustered_far_apart_targets():
     src[1] = tgt[96]
     scans, counts = eng.pack_scans([src, tgt])
     pairs = np.array([[0, 1]], np.int32)
-    run = lambda: eng.run_icp_batch(scans, counts, pairs, None, epsilon=1e-9, max_iters=12,
-                                    return_correspondences=True)
+    run = lambda flags: eng.run_icp_batch(scans, counts, pairs, None, epsilon=1e-9, max_iters=12,
+                                          return_correspondences=True, flags=flags)
     a, e = _both(run)
     _same(a, e)
     T, err, corr, passes = orc.run_icp_info(src, tgt, np.eye(4), epsilon=1e-9, max_iters=12, nn="brute")
@@ -138,8 +142,8 @@ def test_pruned_equals_exhaustive_with_large_offsets_and_normalised_error():
     init[:, 2, :] = torch.tensor([0.0, 0.0, 1.0, 0.0], dtype=torch.float64)
     init[:, 3, :] = torch.tensor([0.0, 0.0, 0.0, 1.0], dtype=torch.float64)
     init[:, :2, 2] = 0.0
-    run = lambda: eng.run_icp_batch(scans, counts, b["pairs"], init, epsilon=eps, normalize_error=norm,
-                                    return_correspondences=True)
+    run = lambda flags: eng.run_icp_batch(scans, counts, b["pairs"], init, epsilon=eps, normalize_error=norm,
+                                          return_correspondences=True, flags=flags)
     a, e = _both(run)
     _same(a, e)
     assert bool(((a.status == 0) | (a.status == 2)).all())
@@ -152,7 +156,11 @@ def test_pruned_handles_non_finite_points_like_exhaustive():
     src = tgt[:64] + 0.01
     src[7, 0] = np.nan
     scans, counts = eng.pack_scans([src, tgt])
-    run = lambda: eng.run_icp_batch(scans, counts, np.array([[0, 1]], np.int32), None, epsilon=1e-3, max_iters=5)
-    a, e = _both(run)
+    from lidar_slam_b200 import engine
+    run = lambda flags: eng.run_icp_batch(scans, counts, np.array([[0, 1]], np.int32), None, epsilon=1e-3,
+                                          max_iters=5, flags=flags)
+    a, e = run(0), run(engine.FLAG_EXHAUSTIVE)
+    n = run(engine.FLAG_NO_PRUNE)
+    assert int(n.status[0]) == 3 and int(n.iters[0]) == int(a.iters[0])
     assert int(a.status[0]) == int(e.status[0]) == 3       # non-finite error stops the pair
     assert int(a.iters[0]) == int(e.iters[0])
