@@ -156,9 +156,34 @@ int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans
                          int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
                          double* const* peer_pose_out, int n_peers, long long peer_row0);
 
+/* The fused multi-GPU pose exchange of a launch (see b200icp_run_exchange), with optional ARRIVAL
+ * FLAGS that replace the cross-rank barrier after the launch: the thread that retires the launch's
+ * last pair stores flag_value -- after all pose rows, release at system scope -- into the uint32 at
+ * byte offset flag_offset_bytes + 4 * flag_index of EVERY peer buffer.  A consumer on any rank waits
+ * until its own buffer holds flag_value in the words of all ranks (b200icp_exchange_wait) and may
+ * then read every row.  flag_offset_bytes = 0: no flags (the caller synchronises the ranks). */
+typedef struct b200icp_exchange {
+  double* const* peer_pose_out; /* HOST array of n_peers device pointers (32-byte aligned)        */
+  int n_peers;                  /* <= 16                                                          */
+  long long peer_row0;          /* row of this launch's pair 0 in every gather buffer             */
+  long long flag_offset_bytes;  /* multiple of 4, beyond the rows; 0 = no arrival flags           */
+  int flag_index;               /* this rank's flag word                                          */
+  unsigned int flag_value;      /* value that announces this launch (e.g. step number + 1)        */
+} b200icp_exchange;
+
+/* Stream-ordered wait for the arrival flags: returns (on the stream) once the n_flags uint32 words at
+ * `flags` (this rank's own buffer + flag_offset_bytes) all hold a value >= `value`, or after
+ * timeout_ms milliseconds, in which case *timed_out (device uint32, may be NULL) is set to 1. */
+int b200icp_exchange_wait(const unsigned int* flags, int n_flags, unsigned int value, int timeout_ms,
+                          unsigned int* timed_out, void* stream);
+
+/* Stream-ordered raise of this rank's arrival flag on every peer buffer (what the kernels do when
+ * their last pair retires), for callers that split one logical launch over several streams. */
+int b200icp_exchange_signal(const b200icp_exchange* exchange, void* stream);
+
 /* The general device entry: b200icp_run with every optional extra in one signature.
  * ready_scans     NULL, or the gate of b200icp_run_gated;
- * peer_pose_out / n_peers / peer_row0   NULL, 0, 0, or the exchange of b200icp_run_exchange;
+ * exchange        NULL, or the fused pose exchange (above);
  * flags           B200ICP_FLAG_* (0 = the shipped defaults).
  * b200icp_run, b200icp_run_gated and b200icp_run_exchange are this entry with flags = 0. */
 int b200icp_run_ex(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
@@ -166,8 +191,7 @@ int b200icp_run_ex(const double* scans, const int32_t* counts, int n_scans, int 
                    const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                    double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                    int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
-                   const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
-                   long long peer_row0, unsigned flags);
+                   const unsigned int* ready_scans, const b200icp_exchange* exchange, unsigned flags);
 
 /* b200icp_run_ex over a pool of RANGES instead of points (planar kernel only: n_beams <= 2048).
  * Replaces get_lidar_data (modules/localization.py:252-307) AND run_icp (modules/icp.py:123-189)
@@ -189,8 +213,8 @@ int b200icp_run_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_
                        const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                        double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                        int32_t* corr_out, int32_t* counts_out, void* workspace, size_t workspace_bytes,
-                       void* stream, const unsigned int* ready_scans, double* const* peer_pose_out,
-                       int n_peers, long long peer_row0, unsigned flags);
+                       void* stream, const unsigned int* ready_scans, const b200icp_exchange* exchange,
+                       unsigned flags);
 
 /* b200icp_run for callers that live in HOST memory, like the reference (numpy arrays): every
  * pointer below is a host pointer (pinned or pageable), results included; the arguments mean
@@ -208,16 +232,14 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
                      const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                      double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                      int32_t* corr_out);
-/* b200icp_run_host with the optional extras: the fused multi-GPU pose exchange
- * (peer_pose_out / n_peers / peer_row0 as in b200icp_run_exchange: a HOST array of peer-mapped
- * DEVICE pointers; NULL, 0, 0 = none) and the launch flags (B200ICP_FLAG_*).  With peers the same
- * entry serves one and several GPUs: every rank calls it on its shard of the pair list. */
+/* b200icp_run_host with the optional extras: the fused multi-GPU pose exchange (`exchange`, NULL =
+ * none; its peer pointers are peer-mapped DEVICE pointers) and the launch flags (B200ICP_FLAG_*).
+ * With an exchange the same entry serves one and several GPUs: every rank calls it on its shard. */
 int b200icp_run_host_ex(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
                         const int32_t* pairs, const double* init, const double* epsilon,
                         const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                         double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
-                        int32_t* corr_out, double* const* peer_pose_out, int n_peers, long long peer_row0,
-                        unsigned flags);
+                        int32_t* corr_out, const b200icp_exchange* exchange, unsigned flags);
 
 /* b200icp_run_ranges for callers that live in HOST memory: the reference's pipeline
  * get_lidar_data -> poses_from_scan_matching (modules/localization.py:252-307, then :95-134) with
@@ -225,7 +247,7 @@ int b200icp_run_host_ex(const double* scans, const int32_t* counts, int n_scans,
  * float32 copy, ranges_dtype 1).  Half (a quarter) of the bytes of the point pool cross PCIe; the
  * range rows are streamed in slices under ONE gated launch whose kernel builds the scans
  * (bit-identical to get_lidar_data) as it stages each pair.  All pointers are HOST pointers except
- * the entries of peer_pose_out.  counts_out [n_scans] int32 or NULL: valid beams per scan (-1 for a
+ * the peer pointers inside `exchange`.  counts_out [n_scans] int32 or NULL: valid beams per scan (-1 for a
  * scan no pair referenced).  Initial transforms must keep the plane (status 5 otherwise).
  * Synchronous; calls on one device are serialised. */
 int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
@@ -233,8 +255,8 @@ int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, i
                             const int32_t* pairs, const double* init, const double* epsilon,
                             const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                             double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
-                            int32_t* corr_out, int32_t* counts_out, double* const* peer_pose_out, int n_peers,
-                            long long peer_row0, unsigned flags);
+                            int32_t* corr_out, int32_t* counts_out, const b200icp_exchange* exchange,
+                            unsigned flags);
 int b200icp_host_release(void);
 
 /* One exact nearest-neighbour pass, exposed on its own for tests and for the

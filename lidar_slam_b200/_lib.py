@@ -31,19 +31,20 @@ SIGNATURES = {
                                   ctypes.c_longlong]),
     "b200icp_run_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
-                               c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_int,
-                               ctypes.c_longlong, ctypes.c_uint]),
+                               c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, ctypes.c_uint]),
     "b200icp_run_ranges": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double, c_double, c_double,
                                    c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_double,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
-                                   c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, ctypes.c_uint]),
+                                   c_void_p, c_void_p, c_void_p, ctypes.c_uint]),
     "b200icp_run_host_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
-                                    c_void_p, c_void_p, c_int, ctypes.c_longlong, ctypes.c_uint]),
+                                    c_void_p, c_void_p, ctypes.c_uint]),
     "b200icp_run_host_ranges": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double, c_double,
                                         c_double, c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                         c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                                        c_void_p, c_int, ctypes.c_longlong, ctypes.c_uint]),
+                                        c_void_p, ctypes.c_uint]),
+    "b200icp_exchange_wait": (c_int, [c_void_p, c_int, ctypes.c_uint, c_int, c_void_p, c_void_p]),
+    "b200icp_exchange_signal": (c_int, [c_void_p, c_void_p]),
     "b200icp_run_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),
@@ -82,6 +83,22 @@ def flag_slices(n: int) -> int:
 
 def flag_chunks(n: int) -> int:
     return (int(n) & 0xff) << 16
+
+
+class Exchange(ctypes.Structure):
+    """b200icp_exchange (include/b200icp.h)."""
+    _fields_ = [("peer_pose_out", c_void_p), ("n_peers", c_int), ("peer_row0", ctypes.c_longlong),
+                ("flag_offset_bytes", ctypes.c_longlong), ("flag_index", c_int), ("flag_value", ctypes.c_uint)]
+
+
+def make_exchange(peer_pose_ptrs, peer_row0=0, flag_offset_bytes=0, flag_index=0, flag_value=0):
+    """(Exchange, keep-alive) for a list of peer-mapped device pointers; None when there are no peers."""
+    if not peer_pose_ptrs:
+        return None, None
+    arr = (c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
+    ex = Exchange(ctypes.cast(arr, c_void_p), len(peer_pose_ptrs), int(peer_row0), int(flag_offset_bytes),
+                  int(flag_index), int(flag_value))
+    return ex, arr
 
 
 _lib = None

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200icp.so")
 SOURCES = ["api.cu", "host_api.cu", "voxel.cu", "scan_build.cu", "ogm.cu", "texture.cu"]
-HEADERS = ["icp_common.cuh", "icp2d.cuh", "icp2d_rows.cuh", "icp3d.cuh", "kabsch3.cuh",
+HEADERS = ["icp_common.cuh", "icp2d.cuh", "icp2d_rows.cuh", "icp3d_flow.cuh", "kabsch3.cuh",
            os.path.join("..", "..", "include", "b200icp.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -5,7 +5,7 @@
 
 #include "icp2d.cuh"
 #include "icp2d_rows.cuh"
-#include "icp3d.cuh"
+#include "icp3d_flow.cuh"
 
 using namespace b200icp;
 
@@ -26,15 +26,7 @@ unsigned b200icp::env_flags() {
 namespace {
 
 constexpr int kMax2d = 2048;  // 6-bit block id x 32 targets
-// General kernel: each resident cluster keeps an fp32 copy of its current target in the
-// workspace (read back by TMA).  At most this many clusters are launched (2 CTAs x 148 SMs).
-constexpr int kMaxClusterSlots = 296;
-
 inline bool uses_general_kernel(int n_max, int dim) { return !(dim == 2 && n_max <= kMax2d); }
-inline size_t tgt32_slot_floats(int n_max) {
-  const size_t np32 = (((size_t)n_max + 31) / 32) * 32;
-  return ((np32 * 3 + 31) / 32) * 32;          // 128-byte multiple
-}
 
 struct DeviceInfo {
   int sms;
@@ -54,7 +46,6 @@ DeviceInfo device_info() {
 // B200ICP_FLAG_EXHAUSTIVE selects the sweep that evaluates every (source, target) candidate
 // (same results; kept for A/B timing and as the FP32-issue-rate figure of the inner loop).
 // Default: the block-pruned sweep (icp2d.cuh).
-inline bool prune_enabled(unsigned flags) { return !(flags & B200ICP_FLAG_EXHAUSTIVE); }
 
 template <int R, int W, int MINB, bool PRUNE>
 int launch2d_variant(const RunParams& p, cudaStream_t stream, int sms) {
@@ -96,46 +87,48 @@ int launch_rows(const RunParams& p, cudaStream_t stream, int sms, unsigned flags
                : launch_rows_variant<W, R, MINB, false, false>(p, stream, sms);
 }
 
-int launch3d(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, int sms) {
-  const long long slots_needed = p.n_pairs < kMaxClusterSlots ? p.n_pairs : kMaxClusterSlots;
-  p.tgt32_stride = (long long)tgt32_slot_floats(p.n_max);
-  if (workspace_bytes < 256 + (size_t)slots_needed * p.tgt32_stride * sizeof(float)) return B200ICP_ERR_WORKSPACE;
-  p.tgt32 = reinterpret_cast<float*>(static_cast<char*>(workspace) + 256);
-  constexpr int R = 4, TH = 256;
-  auto kern = icp3d_kernel<R, TH>;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
-    return B200ICP_ERR_CUDA;
-  // CTAs per pair (cluster size).  Pass counts differ a lot between pairs (2 ... hundreds), so a
-  // batch of few big clouds is bounded by its slowest pair unless that pair is spread over many
-  // SMs: grow the cluster until the batch offers ~4 CTAs per resident slot, keeping at least two
-  // rows of TH source points per CTA, at most 16 CTAs (the sm_100 cluster limit).
-  const long long rows = ((long long)p.n_max + TH - 1) / TH;
-  int g = 1;
-  while (g < 16 && (long long)p.n_pairs * g < 8LL * sms && 4LL * g <= rows) g *= 2;
-  if (const char* e = getenv("B200ICP_CLUSTER_SIZE")) {     // tuning knob: 1, 2, 4, 8 or 16
-    const int v = atoi(e);
-    if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) g = v;
+// General kernel (icp3d_flow.cuh): three launches per chunk of <= kFlowMaxPairs pairs on the caller's
+// stream -- setup, prepare (one CTA per referenced scan), the persistent dataflow kernel.
+int launch3d(RunParams p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, int sms, unsigned flags) {
+  const int total = p.n_pairs;
+  const bool prune = !(flags & (B200ICP_FLAG_NO_PRUNE | B200ICP_FLAG_EXHAUSTIVE));
+  const long long row0 = p.peer_row0;
+  for (int b0 = 0; b0 < total; b0 += kFlowMaxPairs) {
+    const int nb = total - b0 < kFlowMaxPairs ? total - b0 : kFlowMaxPairs;
+    RunParams q = p;
+    q.n_pairs = nb;
+    q.pairs = p.pairs + 2 * (size_t)b0;
+    if (p.init) q.init = p.init + 16 * (size_t)b0;
+    if (p.epsilon) q.epsilon = p.epsilon + b0;
+    if (p.normalize) q.normalize = p.normalize + b0;
+    if (p.T_out) q.T_out = p.T_out + 16 * (size_t)b0;
+    if (p.err_out) q.err_out = p.err_out + b0;
+    if (p.iters_out) q.iters_out = p.iters_out + b0;
+    if (p.status_out) q.status_out = p.status_out + b0;
+    if (p.corr_out) q.corr_out = p.corr_out + (size_t)b0 * p.n_max;
+    if (p.dist2_out) q.dist2_out = p.dist2_out + (size_t)b0 * p.n_max;
+    q.peer_row0 = row0 + b0;
+    if (b0 + nb < total) q.flag_off = 0;      // arrival flags: raised by the last launch only (stream order covers the rest)
+    const FlowLayout L = flow_layout(nb, p.n_max);
+    if (workspace_bytes < L.total) return B200ICP_ERR_WORKSPACE;
+    char* ws = static_cast<char*>(workspace);
+    if (b0 > 0 && cudaMemsetAsync(ws, 0, 256, stream) != cudaSuccess) return B200ICP_ERR_CUDA;
+    flow_setup_kernel<<<1, 1024, 0, stream>>>(q, dim, L, ws);
+    const size_t prep_smem = (size_t)16 * kPrepThreads * sizeof(unsigned);
+    flow_prepare_kernel<<<2 * nb, kPrepThreads, prep_smem, stream>>>(q, dim, L, ws);
+    int per_sm = 0;
+    auto kern = prune ? icp3d_flow_kernel<true> : icp3d_flow_kernel<false>;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFlowWarps * 32, 0) != cudaSuccess || per_sm < 1)
+      return B200ICP_ERR_CUDA;
+    long long items = 0;
+    items = (long long)nb * L.max_chunks;
+    long long grid = (long long)per_sm * sms;
+    if (grid > items) grid = items;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, kFlowWarps * 32, 0, stream>>>(q, L, ws);
+    if (cudaGetLastError() != cudaSuccess) return B200ICP_ERR_CUDA;
   }
-  for (; g >= 1; g /= 2) {
-    cudaLaunchConfig_t cfg{};
-    cudaLaunchAttribute attr{};
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = (unsigned)g; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
-    cfg.blockDim = dim3(TH); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
-    cfg.attrs = &attr; cfg.numAttrs = 1;
-    cfg.gridDim = dim3((unsigned)g);
-    int clusters = 0;
-    if (cudaOccupancyMaxActiveClusters(&clusters, kern, &cfg) != cudaSuccess || clusters < 1) {
-      cudaGetLastError();
-      continue;     // this cluster size cannot be co-scheduled: try a smaller one
-    }
-    long long want = p.n_pairs < clusters ? p.n_pairs : clusters;
-    if (want > kMaxClusterSlots) want = kMaxClusterSlots;
-    cfg.gridDim = dim3((unsigned)(want * g));
-    if (cudaLaunchKernelEx(&cfg, kern, p, dim) != cudaSuccess) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
-    return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
-  }
-  return B200ICP_ERR_CUDA;
+  return B200ICP_OK;
 }
 
 int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cudaStream_t stream, unsigned flags) {
@@ -154,7 +147,21 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (!(flags & B200ICP_FLAG_EXHAUSTIVE) || p.ranges) {
       // row kernel: rows of 32*R source points per warp step; capacity is not a function of W
       if (p.n_max <= 512) return launch_rows<4, 1, 5>(p, stream, d.sms, flags);
-      if (p.n_max <= 1280) return launch_rows<4, 2, 4>(p, stream, d.sms, flags);
+      if (p.n_max <= 1280) {
+#ifdef B200ICP_TUNE_VARIANTS
+        // developer build: CTA shapes for A/B timing, selected by flags bits 24..27
+        switch ((flags >> 24) & 0xfu) {
+          case 1: return launch_rows_variant<6, 2, 4, true, false>(p, stream, d.sms);
+          case 2: return launch_rows_variant<8, 2, 3, true, false>(p, stream, d.sms);
+          case 3: return launch_rows_variant<4, 1, 4, true, false>(p, stream, d.sms);
+          case 4: return launch_rows_variant<8, 1, 4, true, false>(p, stream, d.sms);
+          case 5: return launch_rows_variant<5, 2, 4, true, false>(p, stream, d.sms);
+          case 6: return launch_rows_variant<3, 2, 4, true, false>(p, stream, d.sms);
+          default: break;
+        }
+#endif
+        return launch_rows<4, 2, 4>(p, stream, d.sms, flags);
+      }
       return launch_rows<8, 2, 2>(p, stream, d.sms, flags);
     }
     // exhaustive register-tiled kernel (round 1): W warps, up to R rows of 32 source points per
@@ -164,7 +171,7 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (p.n_max <= 1280) return launch2d_variant<5, 8, 3, false>(p, stream, d.sms);
     return launch2d_variant<8, 8, 2, false>(p, stream, d.sms);
   }
-  return launch3d(p, dim, workspace, workspace_bytes, stream, d.sms);
+  return launch3d(p, dim, workspace, workspace_bytes, stream, d.sms, flags);
 }
 
 __global__ void ffma_probe_kernel(float* sink, int iters) {
@@ -196,6 +203,25 @@ __global__ void pack_poses_kernel(const double* T, const double* err, int n, dou
   reinterpret_cast<double4*>(out)[i] = o;
 }
 
+// Arrival-flag wait of the fused exchange: one thread per flag word, system-scope acquire loads.
+__global__ void exchange_wait_kernel(const unsigned int* flags, int n_flags, unsigned int value,
+                                     unsigned long long timeout_ns, unsigned int* timed_out) {
+  const int k = threadIdx.x;
+  if (k >= n_flags) return;
+  unsigned long long t0 = 0;
+  while (ld_acquire_sys(flags + k) < value) {
+    __nanosleep(200);
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (t0 == 0) t0 = t;
+    else if (t - t0 > timeout_ns) { if (timed_out) *timed_out = 1u; break; }
+  }
+}
+
+__global__ void exchange_signal_kernel(const RunParams p) {
+  if (threadIdx.x == 0) raise_arrival_flags(p);
+}
+
 }  // namespace
 
 extern "C" {
@@ -217,11 +243,23 @@ const char* b200icp_error_string(int code) {
 int b200icp_workspace_bytes(int n_pairs, int n_max, int dim, size_t* bytes_out) {
   if (!bytes_out || n_pairs < 0 || n_max <= 0 || (dim != 2 && dim != 3)) return B200ICP_ERR_BAD_ARG;
   size_t bytes = 256;  // the work-queue counter (padded)
-  if (uses_general_kernel(n_max, dim)) {
-    const size_t slots = (size_t)(n_pairs < kMaxClusterSlots ? n_pairs : kMaxClusterSlots);
-    bytes += slots * tgt32_slot_floats(n_max) * sizeof(float);   // fp32 target copies, one per resident cluster
-  }
+  if (uses_general_kernel(n_max, dim))   // control block, per-pair state, ring, partial sums, one prepared copy per referenced scan
+    bytes = flow_layout(n_pairs < kFlowMaxPairs ? (n_pairs > 0 ? n_pairs : 1) : kFlowMaxPairs, n_max).total;
   *bytes_out = bytes;
+  return B200ICP_OK;
+}
+
+static int apply_exchange(RunParams& p, const b200icp_exchange* ex) {
+  if (!ex) return B200ICP_OK;
+  if (ex->n_peers < 0 || ex->n_peers > kMaxPeers || (ex->n_peers > 0 && !ex->peer_pose_out) || ex->peer_row0 < 0 ||
+      ex->flag_offset_bytes < 0 || (ex->flag_offset_bytes & 3) || ex->flag_index < 0)
+    return B200ICP_ERR_BAD_ARG;
+  p.n_peers = ex->n_peers; p.peer_row0 = ex->peer_row0;
+  p.flag_off = ex->n_peers > 0 ? ex->flag_offset_bytes : 0; p.flag_idx = ex->flag_index; p.flag_val = ex->flag_value;
+  for (int k = 0; k < ex->n_peers; ++k) {
+    if (!ex->peer_pose_out[k] || (reinterpret_cast<uintptr_t>(ex->peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
+    p.peer_out[k] = ex->peer_pose_out[k];
+  }
   return B200ICP_OK;
 }
 
@@ -230,25 +268,20 @@ static int run_common(const double* scans, const int32_t* counts, int n_scans, i
                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                       int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
-                      double* const* peer_pose_out, int n_peers, long long peer_row0,
+                      const b200icp_exchange* exchange,
                       const unsigned int* ready_scans = nullptr, unsigned flags = 0) {
   if (!init || !epsilon || !normalize || !T_out || max_iters < 0) return B200ICP_ERR_BAD_ARG;
   if (ready_scans && uses_general_kernel(n_max, dim)) return B200ICP_ERR_BAD_ARG;   // planar kernel only
-  if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && !peer_pose_out) || peer_row0 < 0)
-    return B200ICP_ERR_BAD_ARG;
   RunParams p{};
   p.scans = scans; p.counts = counts; p.n_scans = n_scans; p.n_max = n_max;
   p.pairs = pairs; p.init = init; p.epsilon = epsilon; p.normalize = normalize;
   p.n_pairs = n_pairs; p.max_iters = max_iters; p.stopping_thresh = stopping_thresh;
   p.T_out = T_out; p.err_out = err_out; p.iters_out = iters_out; p.status_out = status_out;
   p.corr_out = corr_out; p.dist2_out = nullptr; p.nearest_only = 0;
-  p.n_peers = n_peers; p.peer_row0 = peer_row0;
   p.ready_scans = ready_scans;
   p.gate_timeout_ns = 5000000000ull;
-  for (int k = 0; k < n_peers; ++k) {
-    if (!peer_pose_out[k] || (reinterpret_cast<uintptr_t>(peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
-    p.peer_out[k] = peer_pose_out[k];
-  }
+  const int rc_ex = apply_exchange(p, exchange);
+  if (rc_ex != B200ICP_OK) return rc_ex;
   return dispatch(p, dim, workspace, workspace_bytes, static_cast<cudaStream_t>(stream), flags);
 }
 
@@ -257,11 +290,10 @@ int b200icp_run_ex(const double* scans, const int32_t* counts, int n_scans, int 
                    const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                    double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                    int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
-                   const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
-                   long long peer_row0, unsigned flags) {
+                   const unsigned int* ready_scans, const b200icp_exchange* exchange, unsigned flags) {
   return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
                     stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
-                    workspace_bytes, stream, peer_pose_out, n_peers, peer_row0, ready_scans, flags);
+                    workspace_bytes, stream, exchange, ready_scans, flags);
 }
 
 int b200icp_run_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
@@ -270,14 +302,12 @@ int b200icp_run_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_
                        const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                        double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                        int32_t* corr_out, int32_t* counts_out, void* workspace, size_t workspace_bytes,
-                       void* stream, const unsigned int* ready_scans, double* const* peer_pose_out,
-                       int n_peers, long long peer_row0, unsigned flags) {
+                       void* stream, const unsigned int* ready_scans, const b200icp_exchange* exchange,
+                       unsigned flags) {
   if (!ranges || (ranges_dtype != 0 && ranges_dtype != 1) || !cos_tab || !sin_tab || n_beams <= 0 ||
       n_beams > kMax2d || !init || !epsilon || !normalize || !T_out || max_iters < 0)
     return B200ICP_ERR_BAD_ARG;
   if ((reinterpret_cast<uintptr_t>(ranges) & (ranges_dtype ? 3u : 7u)) != 0) return B200ICP_ERR_BAD_ARG;
-  if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && !peer_pose_out) || peer_row0 < 0)
-    return B200ICP_ERR_BAD_ARG;
   RunParams p{};
   p.ranges = ranges; p.ranges_f32 = ranges_dtype; p.n_beams = n_beams; p.cos_tab = cos_tab; p.sin_tab = sin_tab;
   p.range_min = range_min; p.range_max = range_max; p.off_x = off_x; p.off_y = off_y; p.counts_out = counts_out;
@@ -285,12 +315,10 @@ int b200icp_run_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_
   p.pairs = pairs; p.init = init; p.epsilon = epsilon; p.normalize = normalize;
   p.n_pairs = n_pairs; p.max_iters = max_iters; p.stopping_thresh = stopping_thresh;
   p.T_out = T_out; p.err_out = err_out; p.iters_out = iters_out; p.status_out = status_out;
-  p.corr_out = corr_out; p.n_peers = n_peers; p.peer_row0 = peer_row0;
+  p.corr_out = corr_out;
   p.ready_scans = ready_scans; p.gate_timeout_ns = 5000000000ull;
-  for (int k = 0; k < n_peers; ++k) {
-    if (!peer_pose_out[k] || (reinterpret_cast<uintptr_t>(peer_pose_out[k]) & 31u)) return B200ICP_ERR_BAD_ARG;
-    p.peer_out[k] = peer_pose_out[k];
-  }
+  const int rc_ex = apply_exchange(p, exchange);
+  if (rc_ex != B200ICP_OK) return rc_ex;
   return dispatch(p, 2, workspace, workspace_bytes, static_cast<cudaStream_t>(stream), flags);
 }
 
@@ -301,7 +329,7 @@ int b200icp_run(const double* scans, const int32_t* counts, int n_scans, int n_m
                 int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream) {
   return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
                     stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
-                    workspace_bytes, stream, nullptr, 0, 0);
+                    workspace_bytes, stream, nullptr);
 }
 
 int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
@@ -310,9 +338,10 @@ int b200icp_run_exchange(const double* scans, const int32_t* counts, int n_scans
                          double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                          int32_t* corr_out, void* workspace, size_t workspace_bytes, void* stream,
                          double* const* peer_pose_out, int n_peers, long long peer_row0) {
+  const b200icp_exchange ex{peer_pose_out, n_peers, peer_row0, 0, 0, 0u};
   return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
                     stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
-                    workspace_bytes, stream, peer_pose_out, n_peers, peer_row0);
+                    workspace_bytes, stream, &ex);
 }
 
 int b200icp_run_gated(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
@@ -323,9 +352,10 @@ int b200icp_run_gated(const double* scans, const int32_t* counts, int n_scans, i
                       const unsigned int* ready_scans, double* const* peer_pose_out, int n_peers,
                       long long peer_row0) {
   if (!ready_scans) return B200ICP_ERR_BAD_ARG;
+  const b200icp_exchange ex{peer_pose_out, n_peers, peer_row0, 0, 0, 0u};
   return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
                     stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, workspace,
-                    workspace_bytes, stream, peer_pose_out, n_peers, peer_row0, ready_scans);
+                    workspace_bytes, stream, &ex, ready_scans);
 }
 
 int b200icp_nearest(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
@@ -343,6 +373,23 @@ int b200icp_pack_poses(const double* T, const double* err, int n, double* out, v
   if (!T || !out || n < 0) return B200ICP_ERR_BAD_ARG;
   if (n == 0) return B200ICP_OK;
   pack_poses_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(T, err, n, out);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+
+int b200icp_exchange_wait(const unsigned int* flags, int n_flags, unsigned int value, int timeout_ms,
+                          unsigned int* timed_out, void* stream) {
+  if (!flags || n_flags <= 0 || n_flags > kMaxPeers || timeout_ms <= 0) return B200ICP_ERR_BAD_ARG;
+  exchange_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n_flags, value,
+                                                                        (unsigned long long)timeout_ms * 1000000ull, timed_out);
+  return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
+}
+
+int b200icp_exchange_signal(const b200icp_exchange* exchange, void* stream) {
+  if (!exchange || exchange->n_peers <= 0 || exchange->flag_offset_bytes <= 0) return B200ICP_ERR_BAD_ARG;
+  RunParams p{};
+  const int rc = apply_exchange(p, exchange);
+  if (rc != B200ICP_OK) return rc;
+  exchange_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(p);
   return cudaGetLastError() == cudaSuccess ? B200ICP_OK : B200ICP_ERR_CUDA;
 }
 

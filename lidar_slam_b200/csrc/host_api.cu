@@ -107,7 +107,7 @@ struct HostIo {
   const int32_t* pairs; const double* init; const double* epsilon; const uint8_t* normalize;
   int n_pairs, max_iters; double stopping_thresh;
   double* T_out; double* err_out; int32_t* iters_out; int32_t* status_out; int32_t* corr_out;
-  double* const* peers; int n_peers; long long peer_row0;
+  const b200icp_exchange* exchange;
   unsigned flags;
 };
 
@@ -207,7 +207,7 @@ int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
         io.max_iters, io.stopping_thresh, reinterpret_cast<double*>(d + o.T), reinterpret_cast<double*>(d + o.err),
         reinterpret_cast<int32_t*>(d + o.iters), reinterpret_cast<int32_t*>(d + o.status),
         io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
-        reinterpret_cast<const unsigned int*>(d + o_flag), io.peers, io.n_peers, io.peer_row0, io.flags);
+        reinterpret_cast<const unsigned int*>(d + o_flag), io.exchange, io.flags);
   } else {
     rc_run = b200icp_run_ranges(
         d + o_pool, pool.kind == 2 ? 1 : 0, pool.n_scans, pool.n_beams, reinterpret_cast<const double*>(d + o_tabs),
@@ -218,7 +218,7 @@ int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
         reinterpret_cast<int32_t*>(d + o.iters), reinterpret_cast<int32_t*>(d + o.status),
         io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) : nullptr,
         pool.counts_out ? reinterpret_cast<int32_t*>(d + o_counts) : nullptr, d + o_ws, ws_bytes, a.comp[0],
-        reinterpret_cast<const unsigned int*>(d + o_flag), io.peers, io.n_peers, io.peer_row0, io.flags);
+        reinterpret_cast<const unsigned int*>(d + o_flag), io.exchange, io.flags);
   }
   B200_TRY(cudaEventRecord(a.done[0], a.comp[0]));
   B200_TRY(cudaStreamWaitEvent(a.copy, a.done[0], 0));
@@ -296,6 +296,12 @@ int run_chunked(HostArena& a, const HostPool& pool, const HostIo& io, int run_di
     cudaStream_t st = a.comp[c & 1];
     B200_TRY(cudaStreamWaitEvent(st, a.ready[c], 0));
     const size_t b0 = (size_t)lo[c];
+    b200icp_exchange ex_c{};
+    if (io.exchange) {      // the chunk's rows; the arrival flags are raised once, after every chunk (below)
+      ex_c = *io.exchange;
+      ex_c.peer_row0 += (long long)b0;
+      ex_c.flag_offset_bytes = 0;
+    }
     rc_run = b200icp_run_ex(reinterpret_cast<const double*>(d + o_scans), reinterpret_cast<const int32_t*>(d + o_counts),
                             pool.n_scans, pool.n_max, run_dim, reinterpret_cast<const int32_t*>(d + o.pairs) + 2 * b0,
                             reinterpret_cast<const double*>(d + o.init) + 16 * b0,
@@ -304,8 +310,7 @@ int run_chunked(HostArena& a, const HostPool& pool, const HostIo& io, int run_di
                             reinterpret_cast<double*>(d + o.T) + 16 * b0, reinterpret_cast<double*>(d + o.err) + b0,
                             reinterpret_cast<int32_t*>(d + o.iters) + b0, reinterpret_cast<int32_t*>(d + o.status) + b0,
                             io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) + b0 * pool.n_max : nullptr,
-                            d + o_ws[c], ws_bytes[c], st, nullptr, io.peers, io.n_peers, io.peer_row0 + (long long)b0,
-                            io.flags);
+                            d + o_ws[c], ws_bytes[c], st, nullptr, io.exchange ? &ex_c : nullptr, io.flags);
     if (rc_run != B200ICP_OK) break;
   }
   for (int k = 0; k < 2; ++k) {   // results back once both compute streams are done
@@ -313,6 +318,10 @@ int run_chunked(HostArena& a, const HostPool& pool, const HostIo& io, int run_di
     B200_TRY(cudaStreamWaitEvent(a.copy, a.done[k], 0));
   }
   if (rc_run == B200ICP_OK) {
+    if (io.exchange && io.exchange->n_peers > 0 && io.exchange->flag_offset_bytes != 0) {
+      const int rc_sig = b200icp_exchange_signal(io.exchange, a.copy);    // all chunks have retired (events above)
+      if (rc_sig != B200ICP_OK) return rc_sig;
+    }
     const int rc_dn = download_results(a, d, o, io, pool.n_max);
     if (rc_dn != B200ICP_OK) return rc_dn;
   }
@@ -325,7 +334,6 @@ int run_host_impl(const HostPool& pool, HostIo io) {
       pool.n_max <= 0 || io.n_pairs < 0 || io.max_iters < 0 || (pool.dim != 2 && pool.dim != 3) ||
       ((size_t)pool.n_max * pool.dim) % 2 != 0)
     return B200ICP_ERR_BAD_ARG;
-  if (io.n_peers < 0 || io.n_peers > 16 || (io.n_peers > 0 && !io.peers) || io.peer_row0 < 0) return B200ICP_ERR_BAD_ARG;
   if (io.n_pairs == 0) return B200ICP_OK;
   io.flags |= b200icp::env_flags();
   int dev = 0;
@@ -355,13 +363,12 @@ int b200icp_run_host_ex(const double* scans, const int32_t* counts, int n_scans,
                         const int32_t* pairs, const double* init, const double* epsilon,
                         const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                         double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
-                        int32_t* corr_out, double* const* peer_pose_out, int n_peers, long long peer_row0,
-                        unsigned flags) {
+                        int32_t* corr_out, const b200icp_exchange* exchange, unsigned flags) {
   if (!counts) return B200ICP_ERR_BAD_ARG;
   HostPool pool{};
   pool.data = scans; pool.kind = 0; pool.n_scans = n_scans; pool.n_max = n_max; pool.dim = dim; pool.counts = counts;
   HostIo io{pairs, init, epsilon, normalize, n_pairs, max_iters, stopping_thresh, T_out, err_out, iters_out,
-            status_out, corr_out, peer_pose_out, n_peers, peer_row0, flags};
+            status_out, corr_out, exchange, flags};
   return run_host_impl(pool, io);
 }
 
@@ -371,7 +378,7 @@ int b200icp_run_host(const double* scans, const int32_t* counts, int n_scans, in
                      double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                      int32_t* corr_out) {
   return b200icp_run_host_ex(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
-                             stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, nullptr, 0, 0, 0u);
+                             stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, nullptr, 0u);
 }
 
 int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
@@ -379,8 +386,8 @@ int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, i
                             const int32_t* pairs, const double* init, const double* epsilon,
                             const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
                             double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
-                            int32_t* corr_out, int32_t* counts_out, double* const* peer_pose_out, int n_peers,
-                            long long peer_row0, unsigned flags) {
+                            int32_t* corr_out, int32_t* counts_out, const b200icp_exchange* exchange,
+                            unsigned flags) {
   if (!cos_tab || !sin_tab || n_beams <= 0 || n_beams > kMax2dPoints || (ranges_dtype != 0 && ranges_dtype != 1))
     return B200ICP_ERR_BAD_ARG;
   HostPool pool{};
@@ -389,7 +396,7 @@ int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, i
   pool.cos_tab = cos_tab; pool.sin_tab = sin_tab; pool.range_min = range_min; pool.range_max = range_max;
   pool.off_x = off_x; pool.off_y = off_y; pool.counts_out = counts_out;
   HostIo io{pairs, init, epsilon, normalize, n_pairs, max_iters, stopping_thresh, T_out, err_out, iters_out,
-            status_out, corr_out, peer_pose_out, n_peers, peer_row0, flags};
+            status_out, corr_out, exchange, flags};
   return run_host_impl(pool, io);
 }
 

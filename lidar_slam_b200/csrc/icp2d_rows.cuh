@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
           const double* T0 = p.init + (size_t)pair * 16;
           store_pose_to_peers(p, pair, T0[3], T0[7], T0[0], T0[4], kNaN);
         }
+        pair_retired(p, p.queue + 6);
       }
       if (p.corr_out)
         for (int j = tid; j < p.n_max; j += W * 32) p.corr_out[(size_t)pair * p.n_max + j] = -1;
@@ -617,6 +618,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
           if (p.iters_out) p.iters_out[pair] = passes;
           if (p.status_out) p.status_out[pair] = status;
           store_pose_to_peers(p, pair, tx, ty, r00, r10, err);
+          pair_retired(p, p.queue + 6);
         }
         if (p.corr_out) {
           // every lane wrote the matches of its own rows; the barrier of the exchange above made

@@ -228,14 +228,17 @@ struct RunParams {
   double* dist2_out;      // nearest-only mode
   int nearest_only;       // 1: single NN pass on untransformed queries, no solve
   unsigned int* queue;    // work counter in the workspace (zeroed before launch)
-  float* tgt32;           // general kernel: per-cluster fp32 copies of the current target (workspace)
-  long long tgt32_stride; // floats per cluster slot
   // fused pose exchange (multi-GPU): when n_peers > 0 the thread that finishes pair b also
   // stores its packed pose row (x, y, theta, error) into row peer_row0 + b of every rank's
   // gather buffer -- peer-mapped device pointers, i.e. plain stores that travel over NVLink.
   double* peer_out[kMaxPeers];
   int n_peers;
   long long peer_row0;
+  // arrival flags (b200icp_exchange): flag_off != 0 -> the thread that retires the launch's last pair
+  // stores flag_val into the uint32 at byte flag_off + 4 * flag_idx of every peer buffer
+  long long flag_off;
+  int flag_idx;
+  unsigned flag_val;
   // gated launch (b200icp_run_gated): scans [0, *ready_scans) of the pool are resident; the value
   // is raised by copies on another stream while the kernel runs.  Null: the whole pool is resident.
   const unsigned int* ready_scans;
@@ -261,6 +264,21 @@ __device__ __forceinline__ void store_pose_to_peers(const RunParams& p, int pair
   row.x = x; row.y = y; row.z = pose_angle(r10, r00); row.w = err;
   for (int k = 0; k < p.n_peers; ++k)
     reinterpret_cast<double4*>(p.peer_out[k])[p.peer_row0 + pair] = row;
+}
+
+__device__ __forceinline__ void raise_arrival_flags(const RunParams& p) {
+  __threadfence_system();
+  for (int k = 0; k < p.n_peers; ++k) {
+    unsigned* f = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(p.peer_out[k]) + p.flag_off) + p.flag_idx;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(p.flag_val) : "memory");
+  }
+}
+// called by the one thread that has just written pair results (and stored its row to the peers):
+// counts retired pairs; the last one announces the launch to every rank
+__device__ __forceinline__ void pair_retired(const RunParams& p, unsigned* counter) {
+  if (p.n_peers <= 0 || p.flag_off == 0) return;
+  __threadfence_system();
+  if (atomicAdd(counter, 1u) == (unsigned)(p.n_pairs - 1)) raise_arrival_flags(p);
 }
 
 }  // namespace b200icp

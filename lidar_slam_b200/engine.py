@@ -187,7 +187,7 @@ def _copy_pool_pipelined(host_pool, dev_pool, pairs_host, dev, launch_chunk):
 
 def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_iters=2000,
                   stopping_thresh=0.0001, normalize_error=False, return_correspondences=False,
-                  planar_fallback=True, peer_pose_ptrs=None, peer_row0=0, flags=0) -> IcpBatchResult:
+                  planar_fallback=True, peer_pose_ptrs=None, peer_row0=0, flags=0, peer_flag=None) -> IcpBatchResult:
     """Align every (source, target) pair of `pairs` in one launch.
 
     scans  [S, n_max, D] float64 (D = 2 or 3), counts [S] int32 (see pack_scans);
@@ -199,6 +199,8 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     peer_pose_ptrs: optional list of peer-mapped device pointers (one gather buffer per rank);
     the kernel then also stores every pair's (x, y, theta, error) row into row peer_row0 + b of
     each buffer (b200icp_run_exchange; see run_icp_sharded).
+    peer_flag: optional (flag_offset_bytes, flag_index, flag_value): arrival flags of the exchange
+    (b200icp_exchange in include/b200icp.h) instead of a cross-rank barrier after the launch.
     flags: B200ICP_FLAG_* (FLAG_EXHAUSTIVE, FLAG_NO_PRUNE: same results, for A/B timing and tests).
 
     Asynchronous on the current stream, with one exception: a big batch whose scan pool is a PINNED
@@ -263,16 +265,15 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
     _last_workspace = ws
 
     def launch(d, scan_t, pair_t, init_t, eps_t, norm_t, T_t, err_t, it_t, st_t, corr_t, nmax, ws=ws, row0=0, gate=None):
-        peers, n_peers = None, 0
-        if peer_pose_ptrs:
-            peers_arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
-            peers, n_peers = ctypes.cast(peers_arr, ctypes.c_void_p), len(peer_pose_ptrs)
+        last = row0 + pair_t.shape[0] >= n_pairs        # chunked launches: only the last one raises the flags
+        fl = peer_flag if (peer_flag and last) else (0, 0, 0)
+        ex, keep = _lib.make_exchange(peer_pose_ptrs, int(peer_row0) + row0, *fl)
         with torch.cuda.device(dev):
             _lib.check(lib.b200icp_run_ex(
                 _ptr(scan_t), _ptr(counts), n_scans, nmax, d, _ptr(pair_t), _ptr(init_t), _ptr(eps_t),
                 _ptr(norm_t), pair_t.shape[0], int(max_iters), float(stopping_thresh), _ptr(T_t),
                 _ptr(err_t), _ptr(it_t), _ptr(st_t), _ptr(corr_t), _ptr(ws), ws.numel(),
-                _stream_ptr(), _ptr(gate), peers, n_peers, int(peer_row0) + row0, int(flags)), "b200icp_run_ex")
+                _stream_ptr(), _ptr(gate), None if ex is None else ctypes.byref(ex), int(flags)), "b200icp_run_ex")
 
     if host_pool is not None and dim == 2 and n_max <= 2048 and (planar_ok or not planar_fallback):
         _copy_pool_gated(host_pool, scans, dev,
@@ -309,7 +310,7 @@ def run_icp_batch(scans, counts, pairs, init_transforms=None, epsilon=0.01, max_
 
 def run_icp_ranges_batch(ranges, pairs, init_transforms=None, epsilon=0.01, max_iters=2000, stopping_thresh=0.0001,
                          normalize_error=False, return_correspondences=False, range_min=0.1, range_max=30.0,
-                         offset_xy=(0.13323, 0.0), peer_pose_ptrs=None, peer_row0=0, flags=0):
+                         offset_xy=(0.13323, 0.0), peer_pose_ptrs=None, peer_row0=0, flags=0, peer_flag=None):
     """run_icp_batch over a pool of lidar RANGES [S, n_beams] (float64, or float32 when every range is
     float32-representable) instead of points: get_lidar_data (modules/localization.py:252-307) is
     fused into the planar kernel's staging (b200icp_run_ranges), bit-identical to
@@ -353,17 +354,14 @@ def run_icp_ranges_batch(ranges, pairs, init_transforms=None, epsilon=0.01, max_
     ws = torch.empty((nbytes.value,), dtype=torch.uint8, device=dev)
     global _last_workspace
     _last_workspace = ws
-    peers, n_peers = None, 0
-    if peer_pose_ptrs:
-        peers_arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
-        peers, n_peers = ctypes.cast(peers_arr, ctypes.c_void_p), len(peer_pose_ptrs)
+    ex, keep = _lib.make_exchange(peer_pose_ptrs, int(peer_row0), *(peer_flag or (0, 0, 0)))
     with torch.cuda.device(dev):
         _lib.check(lib.b200icp_run_ranges(
             _ptr(r), 1 if r.dtype == torch.float32 else 0, n_scans, n_beams, _ptr(tab[0]), _ptr(tab[1]),
             float(range_min), float(range_max), float(offset_xy[0]), float(offset_xy[1]), _ptr(pairs), _ptr(init),
             _ptr(eps), _ptr(norm), n_pairs, int(max_iters), float(stopping_thresh), _ptr(T), _ptr(err), _ptr(iters),
-            _ptr(status), _ptr(corr), _ptr(counts), _ptr(ws), ws.numel(), _stream_ptr(), None, peers, n_peers,
-            int(peer_row0), int(flags)), "b200icp_run_ranges")
+            _ptr(status), _ptr(corr), _ptr(counts), _ptr(ws), ws.numel(), _stream_ptr(), None,
+            None if ex is None else ctypes.byref(ex), int(flags)), "b200icp_run_ranges")
     return IcpBatchResult(T, err, iters, status, corr), counts
 
 

@@ -56,21 +56,15 @@ def _p(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 
 
-def _peer_array(peer_pose_ptrs):
-    if not peer_pose_ptrs:
-        return None, 0
-    arr = (ctypes.c_void_p * len(peer_pose_ptrs))(*[int(q) for q in peer_pose_ptrs])
-    return arr, len(peer_pose_ptrs)
-
-
 def run_icp_batch_host(scans: np.ndarray, counts: np.ndarray, pairs: np.ndarray, init_transforms=None,
                        epsilon=0.01, max_iters: int = 2000, stopping_thresh: float = 1e-4,
                        normalize_error=False, return_correspondences: bool = False, flags: int = 0,
-                       peer_pose_ptrs=None, peer_row0: int = 0) -> HostBatchResult:
+                       peer_pose_ptrs=None, peer_row0: int = 0, peer_flag=None) -> HostBatchResult:
     """run_icp (modules/icp.py:123-189) for every (source, target) row of `pairs` over a padded scan
     pool in host memory; same per-pair semantics and defaults as the reference call.
     flags: B200ICP_FLAG_* (_lib.FLAG_*); peer_pose_ptrs / peer_row0: the fused multi-GPU pose exchange
-    (device pointers of every rank's gather buffer, include/b200icp.h)."""
+    (device pointers of every rank's gather buffer, include/b200icp.h); peer_flag: optional
+    (flag_offset_bytes, flag_index, flag_value) arrival flags."""
     lib = _lib.load()
     scans = np.ascontiguousarray(scans, dtype=np.float64)
     if scans.ndim != 3 or scans.shape[2] not in (2, 3):
@@ -96,12 +90,11 @@ def run_icp_batch_host(scans: np.ndarray, counts: np.ndarray, pairs: np.ndarray,
     iters = np.empty((n_pairs,), dtype=np.int32)
     status = np.empty((n_pairs,), dtype=np.int32)
     corr = np.empty((n_pairs, n_max), dtype=np.int32) if return_correspondences else None
-    peers, n_peers = _peer_array(peer_pose_ptrs)
+    ex, keep = _lib.make_exchange(peer_pose_ptrs, peer_row0, *(peer_flag or (0, 0, 0)))
     _lib.check(lib.b200icp_run_host_ex(_p(scans), _p(counts), n_scans, n_max, dim, _p(pairs), _p(init), _p(eps),
                                        _p(norm), n_pairs, int(max_iters), float(stopping_thresh), _p(T), _p(err),
-                                       _p(iters), _p(status), _p(corr),
-                                       None if peers is None else ctypes.cast(peers, ctypes.c_void_p), n_peers,
-                                       int(peer_row0), int(flags)), "b200icp_run_host_ex")
+                                       _p(iters), _p(status), _p(corr), None if ex is None else ctypes.byref(ex),
+                                       int(flags)), "b200icp_run_host_ex")
     return HostBatchResult(T, err, iters, status, corr)
 
 
@@ -129,7 +122,7 @@ def run_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms=N
                         max_iters: int = 2000, stopping_thresh: float = 1e-4, normalize_error=False,
                         return_correspondences: bool = False, range_min: float = 0.1, range_max: float = 30.0,
                         offset_xy=(0.13323, 0.0), flags: int = 0, peer_pose_ptrs=None, peer_row0: int = 0,
-                        out: Optional[HostRangesWorkspace] = None, tables=None):
+                        peer_flag=None, out: Optional[HostRangesWorkspace] = None, tables=None):
     """get_lidar_data (modules/localization.py:252-307) + run_icp (modules/icp.py:123-189) for every
     (source, target) row of `pairs`, from the synced lidar ranges [S, n_beams] in host memory (float64
     as the reference holds them, or a float32 copy): b200icp_run_host_ranges.  Returns
@@ -155,14 +148,13 @@ def run_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms=N
     eps = _per_pair(epsilon, n_pairs, np.float64)
     norm = _per_pair(normalize_error, n_pairs, np.uint8)
     o = out if out is not None else HostRangesWorkspace(n_pairs, n_scans, n_max, return_correspondences)
-    peers, n_peers = _peer_array(peer_pose_ptrs)
+    ex, keep = _lib.make_exchange(peer_pose_ptrs, peer_row0, *(peer_flag or (0, 0, 0)))
     _lib.check(lib.b200icp_run_host_ranges(
         _p(ranges), 1 if ranges.dtype == np.float32 else 0, n_scans, n_beams, _p(cos_t), _p(sin_t), float(range_min),
         float(range_max), float(offset_xy[0]), float(offset_xy[1]), _p(pairs), _p(init), _p(eps), _p(norm), n_pairs,
         int(max_iters), float(stopping_thresh), _p(o.T), _p(o.err), _p(o.iters), _p(o.status),
         _p(o.corr) if return_correspondences else None, _p(o.counts),
-        None if peers is None else ctypes.cast(peers, ctypes.c_void_p), n_peers, int(peer_row0), int(flags)),
-        "b200icp_run_host_ranges")
+        None if ex is None else ctypes.byref(ex), int(flags)), "b200icp_run_host_ranges")
     return HostBatchResult(o.T, o.err, o.iters, o.status, o.corr if return_correspondences else None), o.counts
 
 

@@ -101,7 +101,7 @@ def test_gated_launch_gives_up_with_status_not_resident():
     p = engine._ptr
     _lib.check(lib.b200icp_run_ex(p(b["scans"]), p(b["counts"]), b["scans"].shape[0], b["scans"].shape[1], 2,
                                   p(b["pairs"]), p(b["init"]), p(eps), p(norm), n, 2000, 1e-4, p(T), p(err), p(iters),
-                                  p(status), None, p(ws), ws.numel(), engine._stream_ptr(), p(gate), None, 0, 0, 0),
+                                  p(status), None, p(ws), ws.numel(), engine._stream_ptr(), p(gate), None, 0),
                "b200icp_run_ex")
     torch.cuda.synchronize()
     st = status.cpu().numpy()
