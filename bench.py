@@ -6,15 +6,20 @@
 
 One "step" = one pass of the hot path over one batch: config 2 of BASELINE.json,
 `main.py --mode scan_matching --dataset 20` -> 4955 consecutive 1081-beam 2-D scan pairs
-(synthetic scans) per GPU; with N > 1 every rank aligns its own
-4955-pair shard (weak scaling) and ONE all-gather returns all relative poses to every rank.
+(synthetic lidar log) per GPU; with N > 1 every rank aligns its own
+4955-pair shard (weak scaling) and the fused exchange returns all relative poses to every rank.
 
-Printed JSON (one line, rank 0): see the keys at the bottom.  `value` is measured with the
-inputs resident in HBM; `e2e` goes through the public host-facing API with pinned HOST
-buffers, H2D and D2H copies inside the timed region.  `roofline` is the fused ICP kernel
-against the FP32 CUDA-core issue rate measured live by the library's FFMA probe;
-`cpu_baseline` is the oracle port of the reference (scipy KD-tree + LAPACK SVD) on the
-host cores.  `--impl reference` times that CPU implementation alone.
+Printed JSON (one line, rank 0).  `value`: inputs (the point pool) resident in HBM.  `e2e`: the
+C ABI's host entry `b200icp_run_host_ranges` -- pinned HOST lidar ranges in (what the reference's
+get_lidar_data + poses_from_scan_matching start from), HOST poses out, H2D and D2H inside the timed
+region, the same call at every N.  `roofline`: the fused planar kernel against the FP32 CUDA-core
+issue rate measured live by the library's FFMA probe (`frac` = share of that rate the kernel's
+EXECUTED candidate arithmetic occupies).  `configs`: the other BASELINE configs (3: mixed odometry +
+loop-closure launch on ragged scans; 1 / 4: 24-yaw sweeps on 3-D clouds of 6 000 / 20 000 points and
+the voxel_downsample case; 5: the 10^6-pair shard, N > 1 only), each with an oracle check on a fixed
+sample and its own CPU baseline.  `cpu_baseline`: the reference's own run_icp (when importable:
+$LIDAR_SLAM_REF, /root/reference, baseline/_ref), else the oracle port, one process per host core.
+`--impl reference` times that CPU implementation alone.
 """
 from __future__ import annotations
 
@@ -36,72 +41,103 @@ if ROOT not in sys.path:
 PAIRS_PER_GPU = 4955          # config 2: dataset 20 has 4956 synced scans -> 4955 pairs
 N_POOLS = 2                   # distinct scan pools rotated between steps (2 x 85.7 MB > 126 MB L2)
 EPSILON, MAX_ITERS, STOP = 1e-3, 2000, 1e-4   # localization.py:120-123 + icp.py defaults
+RANGE_MIN, RANGE_MAX = 0.1, 30.0              # main.py:84 (Hokuyo gate)
 METRIC = "icp_scan_pair_alignments_per_sec"
 UNIT = "pairs/s"
 
 
 # --------------------------------------------------------------------------------------
-# CPU arm: the oracle port of the reference, all host cores (used by cpu_baseline and
-# by --impl reference).  This is the ONLY place bench.py touches oracle/.
+# CPU arm: the reference's own modules/icp.py when it can be imported on this box, else the
+# oracle port of it; all host cores (cpu_baseline and --impl reference).  This is the ONLY place
+# bench.py touches oracle/ apart from the in-run parity samples.
 # --------------------------------------------------------------------------------------
+def find_reference():
+    """Directory holding the reference's modules/icp.py (modules/icp.py:123 run_icp), or None."""
+    for root in (os.environ.get("LIDAR_SLAM_REF"), "/root/reference", os.path.join(ROOT, "baseline", "_ref")):
+        if root and os.path.isfile(os.path.join(root, "modules", "icp.py")):
+            return root
+    return None
+
+
 def _cpu_worker(args):
-    path, lo, hi = args
+    path, lo, hi, ref_root = args
     os.environ["OPENBLAS_NUM_THREADS"] = "1"
     os.environ["OMP_NUM_THREADS"] = "1"
-    from oracle import icp_oracle as orc
+    run_ref = None
+    if ref_root:
+        if ref_root not in sys.path:
+            sys.path.insert(0, ref_root)
+        from modules.icp import run_icp as run_ref      # the unmodified reference
+    else:
+        from oracle import icp_oracle as orc
     scans = np.load(os.path.join(path, "scans.npy"), mmap_mode="r")     # shared page cache
     counts = np.load(os.path.join(path, "counts.npy"))
     pairs = np.load(os.path.join(path, "pairs.npy"))
     init = np.load(os.path.join(path, "init.npy"))
+    eps = np.load(os.path.join(path, "eps.npy"))
+    norm = np.load(os.path.join(path, "norm.npy"))
     t0 = time.perf_counter()
-    passes = 0
     for k in range(lo, hi):
         s, t = pairs[k]
-        _, _, _, n = orc.run_icp_info(np.asarray(scans[s, :counts[s]]), np.asarray(scans[t, :counts[t]]),
-                                      init[k], epsilon=EPSILON, max_iters=MAX_ITERS, stopping_thresh=STOP)
-        passes += n
-    return time.perf_counter() - t0, passes
+        src, tgt = np.asarray(scans[s, :counts[s]]), np.asarray(scans[t, :counts[t]])
+        if run_ref is not None:
+            run_ref(src, tgt, init_transform=init[k], epsilon=float(eps[k]), max_iters=MAX_ITERS,
+                    stopping_thresh=STOP, return_error=True, normalize_error=bool(norm[k]))
+        else:
+            orc.run_icp_info(src, tgt, init[k], epsilon=float(eps[k]), max_iters=MAX_ITERS, stopping_thresh=STOP,
+                             normalize_error=bool(norm[k]))
+    return time.perf_counter() - t0
 
 
-class CpuReference:
-    """The CPU port on `cores` persistent worker processes (one per core).  `sample(seed)`
-    stages the first n_sample pairs of the workload with that seed; `run(seed)` times one
-    pass over them: contiguous shards, wall time of the slowest worker."""
+class CpuArm:
+    """`cores` persistent worker processes (one per core).  run(sample) times one pass over a sample
+    (dict of numpy arrays scans/counts/pairs/init/eps/norm): contiguous shards of the pair list,
+    wall time of the slowest worker."""
 
-    def __init__(self, n_sample, cores=None):
+    def __init__(self, cores=None):
         import multiprocessing as mp
-        cores = cores or os.cpu_count() or 1
-        self.cores = max(1, min(cores, n_sample))
-        self.n_sample = n_sample
-        self.dirs = {}
-        bounds = np.linspace(0, n_sample, self.cores + 1).astype(int)
-        self.shards = [(int(bounds[i]), int(bounds[i + 1])) for i in range(self.cores) if bounds[i + 1] > bounds[i]]
-        self.pool = mp.get_context("spawn").Pool(len(self.shards))
+        self.cores = max(1, cores or os.cpu_count() or 1)
+        self.ref_root = find_reference()
+        self.kind = "reference" if self.ref_root else "port"
+        self.pool = mp.get_context("spawn").Pool(self.cores)
+        self.dirs = []
 
-    def sample(self, seed):
-        from lidar_slam_b200 import synth
-        if seed not in self.dirs:
-            b = synth.odometry_batch(self.n_sample, seed=seed, device="cpu", n_traj=1)
-            path = tempfile.mkdtemp(prefix="b200icp_cpu_")
-            for name in ("scans", "counts", "pairs", "init"):
-                np.save(os.path.join(path, name + ".npy"), b[name].numpy())
-            self.dirs[seed] = path
-        return self.dirs[seed]
+    def describe(self):
+        return ("the reference's own run_icp (modules/icp.py:123, unmodified, from %s)" % self.ref_root
+                if self.ref_root else "oracle port of modules/icp.py (scipy KDTree + numpy SVD; the reference is not on this box)")
 
-    def run(self, seed):
-        path = self.sample(seed)
-        out = self.pool.map(_cpu_worker, [(path, lo, hi) for lo, hi in self.shards], chunksize=1)
-        slowest = max(t for t, _ in out)
-        return {"value": self.n_sample / slowest, "cores": len(self.shards), "pairs": self.n_sample,
-                "seconds": slowest, "mean_passes": sum(p for _, p in out) / self.n_sample}
+    def stage(self, sample):
+        path = tempfile.mkdtemp(prefix="b200icp_cpu_")
+        for name in ("scans", "counts", "pairs", "init", "eps", "norm"):
+            np.save(os.path.join(path, name + ".npy"), np.ascontiguousarray(sample[name]))
+        self.dirs.append(path)
+        return path, len(sample["pairs"])
+
+    def run(self, staged):
+        path, n = staged
+        k = min(self.cores, n)
+        bounds = np.linspace(0, n, k + 1).astype(int)
+        jobs = [(path, int(bounds[i]), int(bounds[i + 1]), self.ref_root) for i in range(k) if bounds[i + 1] > bounds[i]]
+        out = self.pool.map(_cpu_worker, jobs, chunksize=1)
+        return {"pairs": n, "seconds": max(out), "value": n / max(out), "cores": len(jobs)}
 
     def close(self):
         self.pool.close()
         self.pool.join()
-        for path in self.dirs.values():
-            for name in ("scans", "counts", "pairs", "init"):
-                os.remove(os.path.join(path, name + ".npy"))
+        for path in self.dirs:
+            for f in os.listdir(path):
+                os.remove(os.path.join(path, f))
             os.rmdir(path)
+
+
+def _sample_from_batch(b, idx):
+    """numpy CPU-arm sample: the pairs `idx` of a batch dict (tensors or arrays)."""
+    g = lambda x: x.cpu().numpy() if hasattr(x, "cpu") else np.asarray(x)
+    n = len(idx)
+    eps = g(b["epsilon"])[idx] if "epsilon" in b else np.full(n, EPSILON)
+    norm = g(b["normalize"])[idx] if "normalize" in b else np.zeros(n, np.uint8)
+    return {"scans": g(b["scans"]), "counts": g(b["counts"]), "pairs": g(b["pairs"])[idx], "init": g(b["init"])[idx],
+            "eps": eps, "norm": norm}
 
 
 def _cpu_sample_size():
@@ -109,35 +145,45 @@ def _cpu_sample_size():
     return int(min(PAIRS_PER_GPU, max(512, 256 * cores)))
 
 
+def _config2_workload(B):
+    return ("config2: %d consecutive 1081-beam 2-D scan pairs per GPU (main.py --mode scan_matching --dataset 20 shape%s)"
+            % (B, "" if B == PAIRS_PER_GPU else "; --pairs override, config 2 itself has 4955"))
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    n_sample = _cpu_sample_size()
+    from lidar_slam_b200 import synth
+    n_sample = min(args.pairs, _cpu_sample_size())
     if args.steps * n_sample > 40 * 4955:          # keep the whole run within a few minutes
         n_sample = max(256, 40 * 4955 // args.steps)
-    ref = CpuReference(n_sample)
-    ref.run(seed=20)                                # warm-up: imports, page cache, KD-tree code paths
-    vals, secs = [], 0.0
+    arm = CpuArm()
+    staged = []
+    for k in range(N_POOLS):
+        b = synth.odometry_batch(args.pairs, seed=20 + 10 * k, device="cpu", n_traj=1)
+        staged.append(arm.stage(_sample_from_batch(b, np.arange(n_sample))))
+    arm.run(staged[0])                              # warm-up: imports, page cache, KD-tree code paths
+    for _ in range(max(0, args.warmup - 1)):
+        arm.run(staged[1 % N_POOLS])
+    secs, cores = 0.0, 1
     for k in range(args.steps):
-        r = ref.run(seed=20 + 10 * (k % N_POOLS))
-        vals.append(r)
+        r = arm.run(staged[k % N_POOLS])
         secs += r["seconds"]
-    ref.close()
-    value = sum(r["pairs"] for r in vals) / secs
+        cores = r["cores"]
+    arm.close()
+    value = args.steps * n_sample / secs
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "config2: 4955 consecutive 1081-beam 2-D scan pairs (main.py --mode scan_matching "
-                               "--dataset 20 shape)",
+        "config": {"workload": _config2_workload(args.pairs),
                    "epsilon": EPSILON, "max_iters": MAX_ITERS, "stopping_thresh": STOP,
                    "sample": f"first {n_sample} pairs of each step's pool"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": vals[0]["cores"], "kind": "port",
-                         "sample": f"{n_sample} pairs per step x {args.steps} steps, oracle port of modules/icp.py "
-                                   f"(scipy KDTree + numpy SVD), one process per core, slowest worker",
-                         "mean_passes": vals[0]["mean_passes"]},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": arm.kind,
+                         "sample": f"{n_sample} pairs per step x {args.steps} steps, {arm.describe()}, "
+                                   f"one process per core, slowest worker"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -186,13 +232,190 @@ class ClockSampler:
                 "samples": len(rows), "power_w_max": max(float(r[2]) for r in rows)}
 
 
+def _pin_to_gpu_numa_node(index):
+    """Bind this rank's threads (and therefore its first-touch pinned buffers) to the CPUs next to its
+    GPU: with 8 ranks uploading at once the host-memory path is the e2e limiter."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return len(os.sched_getaffinity(0))
+    except Exception:                                  # noqa: BLE001
+        return None
+
+
 # --------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------
+def _time_launches(fn, n, torch):
+    """n launches of fn(), CUDA events around each, mean ms (after one untimed launch)."""
+    fn()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+    for a, b in evs:
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs) / n
+
+
+def _check_against_oracle(res, clouds_of, pairs, init, idx, eps, norm, tol_T, nn="kdtree"):
+    """In-run parity sample: pass counts equal, poses / errors equal to rounding (tests/ hold the full bar)."""
+    from oracle import icp_oracle as orc
+    for k in idx:
+        src, tgt = clouds_of(int(pairs[k][0])), clouds_of(int(pairs[k][1]))
+        To, eo, _, po = orc.run_icp_info(src, tgt, init[k], epsilon=float(eps[k]), max_iters=MAX_ITERS, stopping_thresh=STOP,
+                                         normalize_error=bool(norm[k]), nn=nn)
+        if int(res.iters[k]) != po or np.abs(res.T[k].cpu().numpy() - To).max() > tol_T or \
+                abs(float(res.error[k]) - eo) > 1e-9 * max(abs(eo), 1e-300):
+            return False
+    return True
+
+
+def run_other_configs(engine, synth, torch, peak, arm, dev, world, rank, quick):
+    """BASELINE configs 3, 1 and 4 (and 5 at N > 1) measured in the same run: kernel time with CUDA
+    events, evaluated share of the candidates, an oracle check on a fixed sample, a CPU baseline on a
+    bounded sample.  Rank 0 only (config 5: all ranks)."""
+    out = {}
+    if rank == 0:
+        # ---- config 3: mixed odometry + loop-closure launch on ragged scans -----------------------
+        b = synth.gtsam_batch(PAIRS_PER_GPU, 10, seed=20, device=dev)
+        run3 = lambda flags=0: engine.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=b["epsilon"],
+                                                    normalize_error=b["normalize"], planar_fallback=False, flags=flags)
+        ms = _time_launches(run3, 6, torch)
+        res = run3()
+        tiles = engine.swept_tiles()
+        cn, pr = b["counts"].double(), b["pairs"].long()
+        cand = float((res.iters.double() * cn[pr[:, 0]] * cn[pr[:, 1]]).sum().item())
+        n_odo, n_all = b["n_odometry"], int(pr.shape[0])
+        scans_np, counts_np = b["scans"].cpu().numpy(), b["counts"].cpu().numpy()
+        pairs_np, init_np = b["pairs"].cpu().numpy(), b["init"].cpu().numpy()
+        eps_np, norm_np = b["epsilon"].cpu().numpy(), b["normalize"].cpu().numpy()
+        idx = list(range(0, n_odo, n_odo // 8))[:8] + list(range(n_odo, n_all, (n_all - n_odo) // 8))[:8]
+        ok = _check_against_oracle(res, lambda i: scans_np[i, :counts_np[i]], pairs_np, init_np, idx, eps_np, norm_np, 1e-9)
+        entry = {
+            "workload": "config3: %d odometry pairs (epsilon 1e-3, raw SSE, odometry init) + %d loop-closure pairs (i, i+10) "
+                        "(epsilon 1e-2, normalised error, identity init) on ragged filtered scans (mean %.0f points), ONE launch "
+                        "(main.py:158-172 + localization.py:112-130)" % (n_odo, n_all - n_odo, float(cn.mean().item())),
+            "kernel": "b200icp::icp2d_rows_kernel", "pairs": n_all, "kernel_ms": ms, "value": n_all / (ms * 1e-3), "unit": UNIT,
+            "mean_passes": {"odometry": float(res.iters[:n_odo].double().mean().item()),
+                            "loop_closure": float(res.iters[n_odo:].double().mean().item())},
+            "evaluated_candidate_share": 1024.0 * tiles / cand,
+            "executed_frac": 4.0 * 1024.0 * tiles / (ms * 1e-3) / peak["lane_ffma_per_s"],
+            "all_pairs_converged": bool(((res.status == 0) | (res.status == 2)).all().item()),
+            "parity_sample_ok": ok, "parity_sample": "8 odometry + 8 loop-closure pairs vs oracle/icp_oracle.py (passes equal, |dT| < 1e-9)",
+        }
+        if arm is not None:
+            n_s = min(n_all, _cpu_sample_size())
+            sel = np.unique(np.linspace(0, n_all - 1, n_s).astype(int))       # keeps the 10:1 mix
+            r = arm.run(arm.stage(_sample_from_batch(b, sel)))
+            entry["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": arm.kind,
+                                     "sample": "%d pairs spread evenly over the mixed list, %.1f s" % (len(sel), r["seconds"])}
+        out["config3_gtsam_mixed_batch"] = entry
+        del b, res
+
+        # ---- configs 1 / 4: 24-yaw sweeps on 3-D clouds ---------------------------------------------
+        for name, n_src, n_tgt in (("config1_yaw_sweep_6000", 6000, 4), ("config4_yaw_sweep_20000", 20000, 4)):
+            y = synth.yaw_sweep_batch(n_src, n_tgt, 24, seed=1)
+            pool, counts = engine.pack_scans(y["clouds"])
+            pairs_d, init_d = torch.as_tensor(y["pairs"]).to(dev), torch.as_tensor(y["init"]).to(dev)
+            runy = lambda flags=0: engine.run_icp_batch(pool, counts, pairs_d, init_d, epsilon=1e-3, normalize_error=True,
+                                                        flags=flags)
+            ms = _time_launches(runy, 3 if quick else 5, torch)
+            res = runy()
+            tiles = engine.swept_tiles()
+            cn = counts.double()
+            prl = pairs_d.long()
+            cand = float((res.iters.double() * cn[prl[:, 0]] * cn[prl[:, 1]]).sum().item())
+            n_p = len(y["pairs"])
+            ones, thou = np.ones(n_p, np.uint8), np.full(n_p, 1e-3)
+            idx = [3, 29] if n_src > 10000 else [3, 29, 77]
+            ok = _check_against_oracle(res, lambda i: y["clouds"][i], y["pairs"], y["init"], idx, thou, ones, 1e-8)
+            best = res.error.view(n_tgt, 24).min(dim=1).values
+            entry = {
+                "workload": "%s: %d-point model, %d partial views (~%d points), 24 yaw initialisations each "
+                            "(code/icp_warm_up/test_icp.py:70-91), one launch of %d problems"
+                            % (name.split("_")[0], n_src, n_tgt, int(counts[1]), n_p),
+                "kernel": "b200icp::icp3d_flow_kernel (+ flow_setup, flow_prepare)", "problems": n_p, "ms_per_sweep": ms,
+                "value": n_p / (ms * 1e-3), "unit": UNIT, "mean_passes": float(res.iters.double().mean().item()),
+                "max_passes": int(res.iters.max().item()),
+                "evaluated_candidate_share": 1024.0 * tiles / cand,
+                "executed_frac": 6.0 * 1024.0 * tiles / (ms * 1e-3) / peak["lane_ffma_per_s"],
+                "algorithmic_rate_vs_peak": 6.0 * cand / (ms * 1e-3) / peak["lane_ffma_per_s"],
+                "best_errors_rounded": [round(float(v), 3) for v in best.cpu()],       # test_icp.py:93
+                "parity_sample_ok": ok, "parity_sample": "%d problems vs oracle/icp_oracle.py (passes equal, |dT| < 1e-8)" % len(idx),
+            }
+            if arm is not None:
+                sel = np.arange(24)                                             # one target, all 24 yaws
+                sample = {"scans": pool.cpu().numpy(), "counts": counts.cpu().numpy(), "pairs": y["pairs"][sel],
+                          "init": y["init"][sel], "eps": thou[sel], "norm": ones[sel]}
+                r = arm.run(arm.stage(sample))
+                entry["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": arm.kind,
+                                         "sample": "the 24 yaw problems of target 0, %.1f s" % r["seconds"]}
+            if n_src > 10000:
+                # the > 20 000-point case: both clouds go through voxel_downsample(., 0.005) first (test_icp.py:75-77)
+                from lidar_slam_b200 import callers
+                big = synth.drill_cloud(26000, seed=2)
+                views = [synth.partial_view(big, seed=40 + k, keep=0.8) for k in range(2)]
+                callers.yaw_sweep(big, views)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                _, errs, _ = callers.yaw_sweep(big, views)
+                torch.cuda.synchronize()
+                entry["voxel_case"] = {"workload": "26 000-point model, 2 views of ~20 800 points: voxel_downsample(0.005) of both "
+                                                   "clouds + 48 problems through callers.yaw_sweep (host round trip included)",
+                                       "ms": 1e3 * (time.perf_counter() - t0), "best_errors_rounded": [float(e) for e in errs]}
+            out[name] = entry
+            del pool, counts, res
+    # ---- config 5 (N > 1): the 10^6-pair batch, 10^6 / N pairs per rank, generated on the rank's device ----
+    if world > 1:
+        import torch.distributed as dist
+        per = 1000000 // world
+        b = synth.odometry_batch(per, seed=20 + 1000 * rank, device=dev)
+        pg = engine._peer_gather_buffer(world * per, dev, None)
+
+        def step5():
+            ptrs, flag, parity = pg.begin()
+            r = engine.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=EPSILON, max_iters=MAX_ITERS,
+                                     stopping_thresh=STOP, planar_fallback=False, peer_pose_ptrs=ptrs, peer_row0=rank * per,
+                                     peer_flag=flag)
+            return r, pg.wait(parity)
+        step5()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res, rows = step5()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        mine = engine.pack_poses(res.T, res.error)
+        ok = bool(torch.equal(rows[rank * per:(rank + 1) * per], mine)) and bool(torch.isfinite(rows).all().item())
+        scans_np, counts_np = b["scans"][:66].cpu().numpy(), b["counts"][:66].cpu().numpy()
+        ok = ok and _check_against_oracle(res, lambda i: scans_np[i, :counts_np[i]], b["pairs"][:64].cpu().numpy(),
+                                          b["init"][:64].cpu().numpy(), list(range(0, 64, 4)), np.full(64, EPSILON),
+                                          np.zeros(64, np.uint8), 1e-9)
+        f = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(f, op=dist.ReduceOp.MIN)
+        pg.check()
+        if rank == 0:
+            out["config5_million_pair_batch"] = {
+                "workload": "config5: %d pairs per rank x %d ranks, generated on each rank's device from seed 20 + 1000 rank, "
+                            "all poses on every rank (fused exchange)" % (per, world),
+                "kernel": "b200icp::icp2d_rows_kernel", "pairs": per * world, "ms": float(t.item()),
+                "value": per * world / (float(t.item()) * 1e-3), "unit": UNIT,
+                "parity_sample_ok": bool(f.item()),
+                "parity_sample": "every rank: own rows delivered intact + 16 pairs vs the oracle; all rows finite"}
+        del b
+    return out
+
+
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
-    from lidar_slam_b200 import engine, synth
+    from lidar_slam_b200 import engine, hostapi, scans as scan_build, synth
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -200,79 +423,88 @@ def run_b200_arm(args):
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+    affinity = _pin_to_gpu_numa_node(local) if world > 1 else None
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
     B = args.pairs
-    # ---- workload: N_POOLS distinct config-2 shaped batches per rank, generated on the device ----
-    pools = []
+    # ---- workload: N_POOLS distinct config-2 shaped lidar logs per rank, generated on the device; the
+    # point pool is built from the ranges exactly as get_lidar_data does (bit-identical kernel) -----------
+    pools, host = [], []
     for k in range(N_POOLS):
-        b = synth.odometry_batch(B, seed=20 + 10 * k + 1000 * rank, device=dev, n_traj=1)
-        pools.append({n: b[n].contiguous() for n in ("scans", "counts", "pairs", "init")})
-    host = []
-    for pl in pools:      # pinned host copies for the end-to-end leg
-        host.append({n: t.cpu().pin_memory() for n, t in pl.items()})
-    h2d_bytes = sum(t.numel() * t.element_size() for t in host[0].values())
-    gathered = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
-    # multi-GPU pose exchange: fused peer stores from the ICP kernel's epilogue into every rank's
-    # symmetric-memory buffer (NVLink), or -- if symmetric memory is unavailable -- pack + NCCL.
-    peer = None
+        b = synth.odometry_batch(B, seed=20 + 10 * k + 1000 * rank, device=dev, n_traj=1, with_ranges=True)
+        ranges = b["ranges"].contiguous()
+        scans, counts = scan_build.scans_from_ranges(ranges, RANGE_MIN, RANGE_MAX)
+        pools.append({"scans": scans, "counts": counts, "pairs": b["pairs"].contiguous(), "init": b["init"].contiguous(),
+                      "ranges": ranges})
+        host.append({"ranges": ranges.cpu().pin_memory().numpy(), "pairs": b["pairs"].cpu().pin_memory().numpy(),
+                     "init": b["init"].cpu().pin_memory().numpy()})
+    n_scans, n_beams = pools[0]["ranges"].shape
+    n_max = pools[0]["scans"].shape[1]
+    tables = hostapi.beam_tables(n_beams)
+    host_ws = hostapi.HostRangesWorkspace(B, n_scans, n_max)
+    h2d_bytes = host[0]["ranges"].nbytes + host[0]["pairs"].nbytes + host[0]["init"].nbytes + B * 9 + 2 * n_beams * 8
+    d2h_bytes = B * (128 + 8 + 4 + 4) + n_scans * 4
+
+    # multi-GPU pose exchange: fused peer stores + arrival flags (symmetric memory, NVLink), or -- if
+    # symmetric memory is unavailable -- pack + NCCL all-gather.
+    pg = None
     if world > 1 and args.exchange in ("auto", "peer"):
         try:
-            gathered, peer = engine._peer_gather_buffer(world * B, dev, None)
+            pg = engine._peer_gather_buffer(world * B, dev, None)
         except Exception as exc:               # noqa: BLE001
             if args.exchange == "peer":
                 raise
             sys.stderr.write(f"[bench] symmetric memory unavailable ({exc!r}); using NCCL all-gather\n")
-            peer = None
-        flag = torch.tensor([1 if peer is not None else 0], device=dev)
+        flag = torch.tensor([1 if pg is not None else 0], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)          # all ranks must agree on the mode
         if int(flag.item()) == 0:
-            peer = None
-            gathered = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
+            pg = None
+    gathered = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
     host_out = torch.empty((world * B, 4), dtype=torch.float64).pin_memory()
-    d2h_bytes = host_out.numel() * host_out.element_size()
-
-    def exchange_kw():
-        return dict(peer_pose_ptrs=list(peer.buffer_ptrs), peer_row0=rank * B) if peer is not None else {}
+    if world > 1:
+        d2h_bytes += host_out.numel() * 8
 
     def step_device(k):
+        """config 2 with the point pool resident in HBM; at N > 1 all poses end up on every rank"""
         pl = pools[k % N_POOLS]
-        if peer is not None:
-            peer.barrier(channel=0)            # the previous step's rows have been consumed everywhere
+        kw = {}
+        if pg is not None:
+            ptrs, flag, parity = pg.begin()
+            kw = dict(peer_pose_ptrs=ptrs, peer_row0=rank * B, peer_flag=flag)
         res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
-                                   max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False,
-                                   **exchange_kw())
-        if peer is not None:
-            peer.barrier(channel=1)            # every rank's rows have landed in every buffer
-            return res
-        poses = engine.pack_poses(res.T, res.error)
+                                   max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False, **kw)
+        if pg is not None:
+            return res, pg.wait(parity)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, poses)
-        else:
-            gathered.copy_(poses)
-        return res
+            dist.all_gather_into_tensor(gathered, engine.pack_poses(res.T, res.error))
+            return res, gathered
+        return res, None
 
     def step_e2e(k):
-        hp = host[k % N_POOLS]          # HOST buffers in, HOST poses out, every step
-        if peer is not None:
-            peer.barrier(channel=0)
-        res = engine.run_icp_batch(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
-                                   max_iters=MAX_ITERS, stopping_thresh=STOP, **exchange_kw())
-        if peer is not None:
-            peer.barrier(channel=1)
+        """HOST ranges in, HOST poses out through the C ABI's host entry (the same call at every N)"""
+        hp = host[k % N_POOLS]
+        kw = {}
+        if pg is not None:
+            ptrs, flag, parity = pg.begin()
+            kw = dict(peer_pose_ptrs=ptrs, peer_row0=rank * B, peer_flag=flag)
+        res, _ = hostapi.run_icp_ranges_host(hp["ranges"], hp["pairs"], hp["init"], epsilon=EPSILON, max_iters=MAX_ITERS,
+                                             stopping_thresh=STOP, range_min=RANGE_MIN, range_max=RANGE_MAX, out=host_ws,
+                                             tables=tables, **kw)
+        if pg is not None:
+            rows = pg.wait(parity)
+            host_out.copy_(rows, non_blocking=True)
+            torch.cuda.synchronize()
+        elif world > 1:
+            local_rows = torch.from_numpy(np.concatenate([res.T[:, 0, 3:4], res.T[:, 1, 3:4],
+                                                          np.arctan2(res.T[:, 1, 0:1], res.T[:, 0, 0:1]),
+                                                          res.error[:, None]], axis=1)).to(dev)
+            dist.all_gather_into_tensor(gathered, local_rows)
             host_out.copy_(gathered, non_blocking=True)
             torch.cuda.synchronize()
-            return
-        poses = engine.pack_poses(res.T, res.error)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, poses)
-            host_out.copy_(gathered, non_blocking=True)
-        else:
-            host_out.copy_(poses, non_blocking=True)
-        torch.cuda.synchronize()        # the caller reads the poses
+        return res
 
     def barrier():
         if world > 1:
@@ -289,12 +521,51 @@ def run_b200_arm(args):
     # ---- FP32 issue-rate probe (roofline denominator), before the timed regions ----
     peak = engine.ffma_peak_tflops()
 
-    # ---- warm-up ----
-    results, tiles = {}, {}
-    for k in range(max(args.warmup, N_POOLS)):
-        results[k % N_POOLS] = step_device(k)
+    # ---- warm-up (+ the checks that make the numbers trustworthy) ----
+    results, tiles, rows_seen = {}, {}, None
+    n_warm = max(args.warmup, N_POOLS, 3)
+    for k in range(n_warm):
+        results[k % N_POOLS], rows_seen = step_device(k)
         tiles[k % N_POOLS] = engine.swept_tiles()      # (32 x 32)-candidate tiles the kernel really swept
     barrier()
+    last_k = (n_warm - 1) % N_POOLS
+    last = results[last_k]
+    ok = all(bool(((r.status == 0) | (r.status == 2)).all().item()) for r in results.values())
+    exchange_check = None
+    if world > 1:
+        # (1) the fused exchange delivers bit for bit what one NCCL all-gather of the packed rows delivers
+        mine = engine.pack_poses(last.T, last.error)
+        nccl_rows = torch.empty((world * B, 4), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(nccl_rows, mine)
+        same = bool(torch.equal(rows_seen, nccl_rows))
+        # (2) a fixed sample of ANOTHER rank's rows equals a local recomputation of that rank's pairs
+        nb_rank = (rank + 1) % world
+        nb = synth.odometry_batch(B, seed=20 + 10 * last_k + 1000 * nb_rank, device=dev, n_traj=1, with_ranges=True)
+        nb_scans, nb_counts = scan_build.scans_from_ranges(nb["ranges"].contiguous(), RANGE_MIN, RANGE_MAX)
+        nb_res = engine.run_icp_batch(nb_scans, nb_counts, nb["pairs"][:64], nb["init"][:64], epsilon=EPSILON,
+                                      max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False)
+        same = same and bool(torch.equal(rows_seen[nb_rank * B:nb_rank * B + 64], engine.pack_poses(nb_res.T, nb_res.error)))
+        f = torch.tensor([1 if same else 0], device=dev)
+        dist.all_reduce(f, op=dist.ReduceOp.MIN)
+        if pg is not None:
+            pg.check()
+        if not bool(f.item()):
+            raise RuntimeError("pose exchange mismatch: fused rows != NCCL all-gather rows (or != a recomputation)")
+        exchange_check = ("peer==nccl bitwise; 64 rows of rank r+1 == local recomputation" if pg is not None
+                          else "nccl; 64 rows of rank r+1 == local recomputation")
+        del nb, nb_scans, nb_res
+    # the ranges entry (what e2e times) == scan build + ICP on the resident pool, bit for bit
+    chk, _ = engine.run_icp_ranges_batch(pools[last_k]["ranges"], pools[last_k]["pairs"], pools[last_k]["init"],
+                                         epsilon=EPSILON, max_iters=MAX_ITERS, stopping_thresh=STOP, range_min=RANGE_MIN,
+                                         range_max=RANGE_MAX)
+    if not (torch.equal(chk.T, last.T) and torch.equal(chk.iters, last.iters) and torch.equal(chk.error, last.error)):
+        raise RuntimeError("b200icp_run_ranges disagrees with scans_from_ranges + b200icp_run on the bench batch")
+    # oracle sample on the bench batch itself
+    pl0 = pools[last_k]
+    sc_np, cn_np = pl0["scans"].cpu().numpy(), pl0["counts"].cpu().numpy()
+    idx2 = list(range(0, B, max(1, B // 16)))[:16]
+    parity2 = _check_against_oracle(last, lambda i: sc_np[i, :cn_np[i]], pl0["pairs"].cpu().numpy(), pl0["init"].cpu().numpy(),
+                                    idx2, np.full(B, EPSILON), np.zeros(B, np.uint8), 1e-9) if rank == 0 else True
 
     # per-step work (identical every time a pool is reused): candidate distance evaluations
     cand = []
@@ -303,18 +574,11 @@ def run_b200_arm(args):
         cn = pl["counts"].double()
         pr = pl["pairs"].long()
         cand.append(float((res.iters.double() * cn[pr[:, 0]] * cn[pr[:, 1]]).sum().item()))
-    mean_passes = float(sum(r.iters.double().mean().item() for r in results.values()) / N_POOLS)
-    ok = all(bool(((r.status == 0) | (r.status == 2)).all().item()) for r in results.values())
-    # the exchange delivered this rank's rows intact and every other rank's rows are finite
-    last = results[(max(args.warmup, N_POOLS) - 1) % N_POOLS]
-    mine = engine.pack_poses(last.T, last.error)
-    exchange_ok = bool(torch.equal(gathered[rank * B:(rank + 1) * B], mine)) and bool(torch.isfinite(gathered).all())
-    if world > 1:
-        flag = torch.tensor([1 if exchange_ok else 0], device=dev)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        exchange_ok = bool(flag.item())
-    if not exchange_ok:
-        raise RuntimeError("pose exchange mismatch: gathered rows differ from the local results")
+    all_iters = torch.cat([r.iters for r in results.values()]).double()
+    passes = {"mean": float(all_iters.mean().item())}
+    for q in (50, 90, 99):
+        passes["p%d" % q] = float(torch.quantile(all_iters, q / 100.0).item())
+    passes["max"] = int(all_iters.max().item())
 
     # ---- timed region 1: inputs resident in HBM ----
     sampler = ClockSampler(local)
@@ -330,7 +594,6 @@ def run_b200_arm(args):
         step_device(k)
     ev1.record()
     barrier()
-    t_wall1 = time.perf_counter()
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
 
     # ---- the dominant kernel alone (CUDA events on the launching stream) ----
@@ -347,30 +610,26 @@ def run_b200_arm(args):
         kernel_ms += kev[k][0].elapsed_time(kev[k][1])
         kernel_cand += cand[k % N_POOLS]
         kernel_eval += 1024.0 * tiles[k % N_POOLS]
-    # the same kernel with the exhaustive sweep (every candidate evaluated; identical results):
-    # the FP32-issue figure of the inner loop itself, timed the same way on a few launches
-    exh_ms, exh_cand, exh_steps = 0.0, 0.0, min(args.steps, 6)
-    exh_res = None
-    for k in range(-1, exh_steps):
-        pl = pools[k % N_POOLS]
-        kev[max(k, 0)][0].record()
-        exh_res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
-                                       max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False,
-                                       flags=engine.FLAG_EXHAUSTIVE)
-        kev[max(k, 0)][1].record()
-        torch.cuda.synchronize()
-        if k >= 0:
-            exh_ms += kev[k][0].elapsed_time(kev[k][1])
-            exh_cand += cand[k % N_POOLS]
-    same = results[(exh_steps - 1) % N_POOLS]
+    # the exhaustive register-tiled kernel (every candidate evaluated; the north-star "brute-force
+    # argmin" variant): the FP32-issue figure of the sweep itself, timed the same way on a few launches
+    exh_steps = min(args.steps, 6)
+    pl = pools[0]
+    run_exh = lambda: engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
+                                           max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False,
+                                           flags=engine.FLAG_EXHAUSTIVE)
+    exh_ms = _time_launches(run_exh, exh_steps, torch)
+    exh_res, same = run_exh(), results[0]
     if not (torch.allclose(exh_res.T, same.T, rtol=1e-11, atol=1e-11) and torch.equal(exh_res.iters, same.iters)
             and torch.allclose(exh_res.error, same.error, rtol=1e-11, atol=0)):
-        raise RuntimeError("pruned and exhaustive sweeps disagree on the bench batch")
+        raise RuntimeError("row kernel and exhaustive kernel disagree on the bench batch")
     clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
 
-    # ---- timed region 2: end to end through the host-facing API ----
-    for k in range(2):
-        step_e2e(k)
+    # ---- timed region 2: end to end through the C ABI's host entry ----
+    e2e_res = None
+    for k in range(3):
+        e2e_res = step_e2e(k)
+    if not np.array_equal(e2e_res.T, results[2 % N_POOLS].T.cpu().numpy()):
+        raise RuntimeError("b200icp_run_host_ranges disagrees with the device entry on the bench batch")
     barrier()
     ev0.record()
     for k in range(args.steps):
@@ -378,29 +637,25 @@ def run_b200_arm(args):
     ev1.record()
     barrier()
     ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+    if pg is not None:
+        pg.check()
 
-    # ---- timed region 3: the C ABI's host-buffer entry (numpy binding, no torch on the path) ----
-    # Every rank aligns its shard from pinned host arrays to host arrays; no pose exchange here
-    # (the caller of this entry is a single-process numpy program like the reference).
-    from lidar_slam_b200 import hostapi
-    host_np = [{k: v.numpy() for k, v in hp.items()} for hp in host]
-    host_res = None
-    for k in range(2):
-        hp = host_np[k % N_POOLS]
-        host_res = hostapi.run_icp_batch_host(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
-                                              max_iters=MAX_ITERS, stopping_thresh=STOP)
-    ref_T = results[1 % N_POOLS].T.cpu().numpy()
-    if not np.array_equal(host_res.T, ref_T):
-        raise RuntimeError("b200icp_run_host disagrees with the device entry on the bench batch")
-    barrier()
-    ev0.record()
-    for k in range(args.steps):
-        hp = host_np[k % N_POOLS]
-        hostapi.run_icp_batch_host(hp["scans"], hp["counts"], hp["pairs"], hp["init"], epsilon=EPSILON,
-                                   max_iters=MAX_ITERS, stopping_thresh=STOP)
-    ev1.record()
-    barrier()
-    ms_host_entry = max_over_ranks(ev0.elapsed_time(ev1))
+    # ---- the un-batched drop-in: run_icp called pair after pair (modules/localization.py:112-130) ----
+    dropin_ms = None
+    if rank == 0:
+        import lidar_slam_b200.icp as dropin
+        clouds = [sc_np[i, :cn_np[i]] for i in range(min(66, n_scans))]
+        n_d = min(64, B)
+        prs, ini = pl0["pairs"][:n_d].cpu().numpy(), pl0["init"][:n_d].cpu().numpy()
+        for rep in range(3):
+            t0 = time.perf_counter()
+            for k in range(n_d):
+                dropin.run_icp(clouds[prs[k][0]], clouds[prs[k][1]], init_transform=ini[k], epsilon=EPSILON)
+            dropin_ms = 1e3 * (time.perf_counter() - t0) / n_d
+
+    # ---- the other BASELINE configs ----
+    arm = CpuArm() if (rank == 0 and not args.no_cpu_baseline) else None
+    configs = {} if args.no_configs else run_other_configs(engine, synth, torch, peak, arm, dev, world, rank, args.steps < 20)
 
     if rank != 0:
         if world > 1:
@@ -409,87 +664,82 @@ def run_b200_arm(args):
 
     value = world * B * args.steps / (ms_total * 1e-3)
     e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
-    lane_instr_per_s = 4.0 * kernel_cand / (kernel_ms * 1e-3)          # 4 FP32-pipe lane-instructions / candidate
+    t_kernel = kernel_ms * 1e-3
+    exec_rate = 4.0 * kernel_eval / t_kernel                   # FP32-pipe lane-instructions really executed per second
+    algo_rate = 4.0 * kernel_cand / t_kernel                   # ... the exhaustive search would have needed
     sms = peak["sms"]
-    nominal = sms * 128 * 1.965e9
-    bytes_per_pair = 2 * 1081 * 16 + 128 + 32                          # two fp64 scans + init + result
-    # End to end.  One GPU: the C ABI's host-buffer entry, the call a numpy program like the reference
-    # makes (pinned host arrays in, T / error / passes / status back in host arrays).  Several GPUs:
-    # the torch engine path, which also delivers every rank's poses to every rank.  Both are
-    # measured at every N and both are reported.
-    host_value = world * B * args.steps / (ms_host_entry * 1e-3)
-    host_d2h = B * (128 + 8 + 4 + 4)
-    engine_path = {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                   "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                   "call": "lidar_slam_b200.engine.run_icp_batch on pinned host tensors (+ pose exchange, poses to host)"}
-    host_path = {"value": host_value, "unit": UNIT, "ms_per_step": ms_host_entry / args.steps,
-                 "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": host_d2h,
-                 "call": "b200icp_run_host via lidar_slam_b200.hostapi (pinned numpy arrays in, numpy arrays out, "
-                         "no torch on the path, no pose exchange)"}
-    if world == 1:
-        e2e = dict(host_path, torch_engine_path=engine_path)
-    else:
-        e2e = dict(engine_path, c_abi_host_entry=host_path)
+    unique_bytes = n_scans * n_max * 16 + B * (8 + 128 + 8 + 1) + B * (128 + 8 + 4 + 4)
     roofline = {
         "bound": "fp32_cuda_core_issue",
-        "kernel": "b200icp::icp2d_kernel (fused ICP: NN sweep + exact resolve + Kabsch + stop tests)",
-        "achieved": lane_instr_per_s * 1.25 / 1e12, "peak": peak["lane_ffma_per_s"] * 2 / 1e12, "unit": "TFLOP/s",
-        "frac": lane_instr_per_s / peak["lane_ffma_per_s"],
-        "frac_note": "SURVEY 8d definition: ALGORITHMIC work = n_src*n_tgt candidate distances per pass x 4 FP32 "
-                     "lane-instructions (5 flops) / measured FFMA lane-instructions per second "
-                     "(b200icp_ffma_probe, this run); achieved/peak in TFLOP/s at 5 flops per candidate vs 2 per "
-                     "FFMA, so achieved/peak = 0.625 * frac.  frac > 1 is possible and expected: the shipped kernel "
-                     "prunes target blocks with exact bounding-box lower bounds and evaluates only "
-                     "`evaluated_candidate_share` of the candidates (results bit-identical to the exhaustive sweep, "
-                     "checked in this run); `executed_frac` is the share of the FP32 issue rate it really occupies, "
-                     "`exhaustive_sweep` the same kernel with every candidate evaluated (B200ICP_SWEEP=exhaustive)",
+        "kernel": "b200icp::icp2d_rows_kernel (fused ICP: pruned NN sweep + exact resolve + Kabsch + stop tests)",
+        "achieved": exec_rate * 1.25 / 1e12, "peak": peak["lane_ffma_per_s"] * 2 / 1e12, "unit": "TFLOP/s",
+        "frac": exec_rate / peak["lane_ffma_per_s"],
+        "frac_note": "share of the measured FFMA lane-instruction rate (b200icp_ffma_probe, this run) occupied by the candidate "
+                     "arithmetic the kernel EXECUTES: evaluated candidates x 4 FP32 lane-instructions (2 FADD, FMUL, FFMA = 5 flops) "
+                     "/ kernel time; achieved/peak are the same in TFLOP/s (5 flops per candidate vs 2 per FFMA: 0.625 x frac). "
+                     "The kernel prunes target blocks with exact bounding-box bounds and evaluates `evaluated_candidate_share` of the "
+                     "n_src x n_tgt candidates per pass (results equal the exhaustive search: tests + the check in this run); "
+                     "`algorithmic_rate_vs_peak` is SURVEY 8d's figure (ALL candidates / time / peak), above 1 for that reason and "
+                     "not a hardware fraction; `exhaustive_kernel` is the north-star brute-force variant (every candidate evaluated)",
+        "algorithmic_rate_vs_peak": algo_rate / peak["lane_ffma_per_s"],
         "evaluated_candidate_share": kernel_eval / kernel_cand,
-        "executed_frac": 4.0 * kernel_eval / (kernel_ms * 1e-3) / peak["lane_ffma_per_s"],
-        "exhaustive_sweep": {"frac": 4.0 * exh_cand / (exh_ms * 1e-3) / peak["lane_ffma_per_s"],
-                             "kernel_ms_per_launch": exh_ms / exh_steps, "launches": exh_steps,
-                             "pairs_per_s": B * exh_steps / (exh_ms * 1e-3),
-                             "results_equal_pruned": True},
-        "achieved_lane_instr_per_s": lane_instr_per_s, "peak_lane_instr_per_s": peak["lane_ffma_per_s"],
+        "exhaustive_kernel": {"kernel": "b200icp::icp2d_kernel<5,8,3,false>", "frac": 4.0 * cand[0] / (exh_ms * 1e-3) / peak["lane_ffma_per_s"],
+                              "kernel_ms_per_launch": exh_ms, "launches": exh_steps, "pairs_per_s": B / (exh_ms * 1e-3),
+                              "results_equal_row_kernel": "pass counts equal, poses/errors equal to 1e-11 (other summation order)"},
+        "peak_lane_instr_per_s": peak["lane_ffma_per_s"],
         "peak_source": "measured live: b200icp_ffma_probe (MEASURED_PEAKS.json has no FP32 CUDA-core figure)",
-        "frac_of_nominal_1965mhz": lane_instr_per_s / nominal,
+        "peak_nominal_lane_instr_per_s": sms * 128 * 1.965e9,
         "kernel_ms_per_launch": kernel_ms / args.steps,
-        "pair_iterations_per_s": kernel_cand / (1081.0 * 1081.0) / (kernel_ms * 1e-3),
-        "hbm_algorithmic_gbs": bytes_per_pair * B * args.steps / (kernel_ms * 1e-3) / 1e9,
+        "pair_iterations_per_s": kernel_cand / (1081.0 * 1081.0) / t_kernel,
+        "hbm_algorithmic_gbs": unique_bytes * args.steps / t_kernel / 1e9,
         "hbm_peak_gbs": _measured_hbm(), "traffic": _ncu_traffic(),
         "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, one ncu --set full capture of this command; profiles/)",
-        "algorithmic_bytes_per_launch": bytes_per_pair * B,
+        "algorithmic_bytes_per_launch": unique_bytes,
+        "algorithmic_bytes_note": "unique bytes: the scan pool once (consecutive pairs share a scan through L2) + pair list, init, "
+                                  "epsilon, normalize + T, error, passes, status",
     }
+    e2e = {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+           "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+           "call": "b200icp_run_host_ranges via lidar_slam_b200.hostapi.run_icp_ranges_host: pinned HOST lidar ranges [%d, %d] float64 "
+                   "(the input of get_lidar_data, localization.py:252-307) + pair list + odometry inits in, T / error / passes / status / "
+                   "counts back in HOST arrays; no torch on the path%s" % (
+                       n_scans, n_beams, "" if world == 1 else "; fused exchange to every rank + arrival-flag wait + all poses to the host"),
+           "results_equal_device_entry": True, "cpus_this_rank_is_bound_to": affinity}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, N_POOLS), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "warmup": n_warm, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32 search + f64 solve", "data": "synthetic",
-        "config": {"workload": "config2: 4955 consecutive 1081-beam 2-D scan pairs per GPU "
-                               "(main.py --mode scan_matching --dataset 20 shape)",
+        "config": {"workload": _config2_workload(B),
                    "pairs_per_gpu": B, "points_per_scan": "1081 beams, ~1075 valid", "epsilon": EPSILON,
-                   "max_iters": MAX_ITERS, "stopping_thresh": STOP, "mean_passes_per_pair": mean_passes,
-                   "l2": f"{N_POOLS} distinct scan pools of 85.7 MB rotated between steps (171 MB > 126 MB L2)",
+                   "max_iters": MAX_ITERS, "stopping_thresh": STOP, "mean_passes_per_pair": passes["mean"],
+                   "passes_per_pair": passes,
+                   "l2": f"{N_POOLS} distinct scan pools of {n_scans * n_max * 16 / 1e6:.1f} MB rotated between steps "
+                         f"(> 126 MB L2 together)",
                    "exchange": ("none (1 GPU)" if world == 1 else
-                                "fused: peer stores of [B,4] f64 rows from the ICP kernel epilogue into every rank's "
-                                "symmetric-memory buffer over NVLink + 2 cross-rank barriers per step"
-                                if peer is not None else "pack_poses + one NCCL all_gather_into_tensor of [B,4] f64 per step"),
-                   "all_pairs_converged": ok},
+                                "fused: peer stores of [B,4] f64 rows + one arrival flag per rank from the ICP kernel's epilogue into "
+                                "every rank's symmetric-memory buffer over NVLink, a stream-ordered flag wait, no host-side barrier"
+                                if pg is not None else "pack_poses + one NCCL all_gather_into_tensor of [B,4] f64 per step"),
+                   "exchange_check": exchange_check, "all_pairs_converged": ok, "parity_sample_ok": parity2,
+                   "parity_sample": "16 pairs of the bench batch vs oracle/icp_oracle.py (passes equal, |dT| < 1e-9)"},
         "e2e": e2e,
-        # icp2d_kernel per step, plus pack_poses_kernel when the exchange is not fused into it
-        "gpu_launches": (1 if peer is not None else 2) * args.steps,
+        # icp2d_rows_kernel per step (+ exchange_wait_kernel at N > 1, or pack_poses_kernel on the NCCL path)
+        "gpu_launches": (1 if world == 1 else 2) * args.steps,
         "roofline": roofline,
+        "configs": configs,
+        "dropin_ms_per_call": dropin_ms,
         "clocks": clocks,
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if arm is not None and world == 1:
         n_sample = min(B, _cpu_sample_size())
-        ref = CpuReference(n_sample)
-        ref.run(seed=20)
-        r = ref.run(seed=20)
-        ref.close()
+        staged = arm.stage(_sample_from_batch(pools[0], np.arange(n_sample)))
+        arm.run(staged)
+        r = arm.run(staged)
         line["cpu_baseline"] = {
-            "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-            "sample": f"first {n_sample} pairs of pool 0, oracle port of modules/icp.py (scipy KDTree + numpy "
-                      f"SVD), one process per core, slowest worker {r['seconds']:.1f} s",
-            "mean_passes": r["mean_passes"]}
+            "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": arm.kind,
+            "sample": f"first {n_sample} pairs of pool 0, {arm.describe()}, one process per core, slowest worker "
+                      f"{r['seconds']:.1f} s"}
+    if arm is not None:
+        arm.close()
     _emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -538,6 +788,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step (default: config 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the configs 1/3/4/5 section")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
                     help="multi-GPU pose exchange: fused peer stores (symmetric memory) or NCCL all-gather")
     args = ap.parse_args()

@@ -59,6 +59,10 @@ extern "C" {
 #define B200ICP_FLAG_NO_PRUNE 0x4u     /* the shipped row kernel with the block bounds switched off
                                           (every block swept, same summation order: bit-identical
                                           results); what the pruned == unpruned tests compare      */
+#define B200ICP_FLAG_LATENCY 0x8u      /* few planar pairs (<= one per SM): 16 warps on each pair instead
+                                          of 4, i.e. shortest time per pair instead of most pairs per
+                                          second.  Another summation order: results equal to rounding
+                                          (1e-13), not bit for bit; b200icp_run_pair_host sets it.    */
 #define B200ICP_FLAG_HOST_CHUNKED 0x2u /* host entries: pair chunks alternating on two streams
                                           instead of ONE gated launch (A/B)                     */
 #define B200ICP_FLAG_SLICES(n) (((unsigned)(n)&0xffu) << 8)  /* host entries: pool slices (0 = 24) */
@@ -257,6 +261,18 @@ int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, i
                             double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
                             int32_t* corr_out, int32_t* counts_out, const b200icp_exchange* exchange,
                             unsigned flags);
+/* run_icp for ONE pair with HOST arrays, the direct C form of the reference call
+ *   run_icp(pc1, pc2, init_transform, epsilon, max_iters, stopping_thresh,
+ *           return_error=True, normalize_error, return_correspondences)   -- modules/icp.py:123-189
+ * as modules/localization.py:120 and main.py:162 make it pair after pair (the un-batched drop-in).
+ * src [n_src, dim], tgt [n_tgt, dim] float64 (dim 2 or 3), init [4,4]; T_out [4,4]; err_out,
+ * iters_out, status_out single values (may be NULL); corr_out [n_src] int32 or NULL.
+ * One pinned staging block, one H2D copy, one launch (a latency-oriented CTA shape: 16 warps on the
+ * pair), one D2H copy.  Synchronous.  A planar pair whose init leaves the plane is lifted to 3-D. */
+int b200icp_run_pair_host(const double* src, int n_src, const double* tgt, int n_tgt, int dim,
+                          const double* init, double epsilon, int max_iters, double stopping_thresh,
+                          int normalize, double* T_out, double* err_out, int32_t* iters_out,
+                          int32_t* status_out, int32_t* corr_out);
 int b200icp_host_release(void);
 
 /* One exact nearest-neighbour pass, exposed on its own for tests and for the

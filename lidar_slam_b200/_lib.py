@@ -48,6 +48,8 @@ SIGNATURES = {
     "b200icp_run_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),
+    "b200icp_run_pair_host": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_double, c_int, c_double,
+                                      c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200icp_host_release": (c_int, []),
     "b200icp_nearest": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -75,6 +77,7 @@ SIGNATURES = {
 FLAG_EXHAUSTIVE = 0x1
 FLAG_HOST_CHUNKED = 0x2
 FLAG_NO_PRUNE = 0x4
+FLAG_LATENCY = 0x8
 
 
 def flag_slices(n: int) -> int:
@@ -128,4 +131,6 @@ def load():
 def check(code: int, what: str):
     if code != 0:
         msg = load().b200icp_error_string(code).decode()
+        if code in (-4, -5):
+            msg += " -- lidar_slam_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback"
         raise RuntimeError(f"{what} failed: {msg} (code {code})")

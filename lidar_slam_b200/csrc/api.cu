@@ -107,6 +107,9 @@ int launch3d(RunParams p, int dim, void* workspace, size_t workspace_bytes, cuda
     if (p.status_out) q.status_out = p.status_out + b0;
     if (p.corr_out) q.corr_out = p.corr_out + (size_t)b0 * p.n_max;
     if (p.dist2_out) q.dist2_out = p.dist2_out + (size_t)b0 * p.n_max;
+#ifdef B200ICP_FLOW_DEBUG
+    if (const char* e = getenv("B200ICP_DEBUG_PTR")) q.dist2_out = reinterpret_cast<double*>(strtoull(e, nullptr, 0));
+#endif
     q.peer_row0 = row0 + b0;
     if (b0 + nb < total) q.flag_off = 0;      // arrival flags: raised by the last launch only (stream order covers the rest)
     const FlowLayout L = flow_layout(nb, p.n_max);
@@ -160,6 +163,8 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
           default: break;
         }
 #endif
+        // few pairs (the un-batched drop-in): 16 warps on each pair, 1-2 rows per warp and pass
+        if ((flags & B200ICP_FLAG_LATENCY) && p.n_pairs <= d.sms) return launch_rows<16, 2, 1>(p, stream, d.sms, flags);
         return launch_rows<4, 2, 4>(p, stream, d.sms, flags);
       }
       return launch_rows<8, 2, 2>(p, stream, d.sms, flags);

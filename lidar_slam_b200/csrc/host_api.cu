@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <mutex>
 
@@ -43,6 +44,8 @@ struct HostArena {
   cudaStream_t copy = nullptr, comp[2] = {nullptr, nullptr};
   cudaEvent_t ready[kMaxChunks] = {}, done[2] = {nullptr, nullptr}, small = nullptr;
   unsigned int* progress_host = nullptr;   // pinned: cumulative row counts, one per slice (+ the gave-up word)
+  char* pin = nullptr;                     // pinned staging of the single-pair entry (grow-only)
+  size_t pin_cap = 0;
   bool ok = false;
 };
 
@@ -398,6 +401,85 @@ int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, i
   HostIo io{pairs, init, epsilon, normalize, n_pairs, max_iters, stopping_thresh, T_out, err_out, iters_out,
             status_out, corr_out, exchange, flags};
   return run_host_impl(pool, io);
+}
+
+// run_icp for ONE pair, host arrays in and out: the un-batched drop-in (modules/icp.py:123-189 as
+// modules/localization.py:120 calls it).  Everything the launch needs travels in ONE pinned block
+// and one host-to-device copy, everything it returns in one device-to-host copy.
+int b200icp_run_pair_host(const double* src, int n_src, const double* tgt, int n_tgt, int dim,
+                          const double* init, double epsilon, int max_iters, double stopping_thresh,
+                          int normalize, double* T_out, double* err_out, int32_t* iters_out,
+                          int32_t* status_out, int32_t* corr_out) {
+  if (!src || !tgt || !init || !T_out || n_src <= 0 || n_tgt <= 0 || max_iters < 0 || (dim != 2 && dim != 3))
+    return B200ICP_ERR_BAD_ARG;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return B200ICP_ERR_NO_DEVICE; }
+  std::lock_guard<std::mutex> lock(g_mutex);
+  HostArena& a = g_arena[dev];
+  if (!arena_init(a)) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
+  int run_dim = dim;
+  if (dim == 2 && !keeps_plane(init)) run_dim = 3;      // the reference's lifting to z = 0 (icp.py:153-156)
+  int n_max = n_src > n_tgt ? n_src : n_tgt;
+  n_max += n_max & 1;
+  const size_t row = (size_t)n_max * run_dim * 8;
+  // input block: [init 128][eps 8][counts 8][pair 8][norm 8 (padded)] [source row][target row]
+  const size_t in_hdr = 160, in_bytes = in_hdr + 2 * row;
+  // output block: [T 128][err 8][iters 4][status 4][corr n_max*4]
+  const size_t out_bytes = 144 + (corr_out ? (size_t)n_max * 4 : 0);
+  size_t ws_bytes = 0;
+  const int rcw = b200icp_workspace_bytes(1, n_max, run_dim, &ws_bytes);
+  if (rcw != B200ICP_OK) return rcw;
+  Carver cv;
+  const size_t o_in = cv.take(in_bytes), o_out = cv.take(out_bytes), o_ws = cv.take(ws_bytes);
+  if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
+  const size_t pin_need = in_bytes + out_bytes + 256;
+  if (pin_need > a.pin_cap) {
+    if (a.pin) cudaFreeHost(a.pin);
+    a.pin = nullptr; a.pin_cap = 0;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&a.pin), pin_need * 2, cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError();
+      return B200ICP_ERR_CUDA;
+    }
+    a.pin_cap = pin_need * 2;
+  }
+  char* h = a.pin;
+  memcpy(h, init, 128);
+  memcpy(h + 128, &epsilon, 8);
+  const int32_t counts[2] = {n_src, n_tgt}, pair[2] = {0, 1};
+  memcpy(h + 136, counts, 8);
+  memcpy(h + 144, pair, 8);
+  memset(h + 152, 0, 8);
+  h[152] = normalize ? 1 : 0;
+  if (run_dim == dim) {
+    memcpy(h + in_hdr, src, (size_t)n_src * dim * 8);
+    memcpy(h + in_hdr + row, tgt, (size_t)n_tgt * dim * 8);
+  } else {      // (x, y) -> (x, y, 0)
+    double* s3 = reinterpret_cast<double*>(h + in_hdr);
+    double* t3 = reinterpret_cast<double*>(h + in_hdr + row);
+    for (int i = 0; i < n_src; ++i) { s3[3 * i] = src[2 * i]; s3[3 * i + 1] = src[2 * i + 1]; s3[3 * i + 2] = 0.0; }
+    for (int i = 0; i < n_tgt; ++i) { t3[3 * i] = tgt[2 * i]; t3[3 * i + 1] = tgt[2 * i + 1]; t3[3 * i + 2] = 0.0; }
+  }
+  char* d = a.base;
+  cudaStream_t st = a.comp[0];
+  B200_TRY(cudaMemcpyAsync(d + o_in, h, in_bytes, cudaMemcpyHostToDevice, st));
+  const int rc_run = b200icp_run_ex(
+      reinterpret_cast<const double*>(d + o_in + in_hdr), reinterpret_cast<const int32_t*>(d + o_in + 136), 2, n_max, run_dim,
+      reinterpret_cast<const int32_t*>(d + o_in + 144), reinterpret_cast<const double*>(d + o_in),
+      reinterpret_cast<const double*>(d + o_in + 128), reinterpret_cast<const uint8_t*>(d + o_in + 152), 1, max_iters,
+      stopping_thresh, reinterpret_cast<double*>(d + o_out), reinterpret_cast<double*>(d + o_out + 128),
+      reinterpret_cast<int32_t*>(d + o_out + 136), reinterpret_cast<int32_t*>(d + o_out + 140),
+      corr_out ? reinterpret_cast<int32_t*>(d + o_out + 144) : nullptr, d + o_ws, ws_bytes, st, nullptr, nullptr,
+      B200ICP_FLAG_LATENCY);
+  if (rc_run != B200ICP_OK) { cudaStreamSynchronize(st); cudaGetLastError(); return rc_run; }
+  char* ho = h + ((in_bytes + 255) / 256) * 256;
+  B200_TRY(cudaMemcpyAsync(ho, d + o_out, out_bytes, cudaMemcpyDeviceToHost, st));
+  B200_TRY(cudaStreamSynchronize(st));
+  memcpy(T_out, ho, 128);
+  if (err_out) memcpy(err_out, ho + 128, 8);
+  if (iters_out) memcpy(iters_out, ho + 136, 4);
+  if (status_out) memcpy(status_out, ho + 140, 4);
+  if (corr_out) memcpy(corr_out, ho + 144, (size_t)n_src * 4);
+  return B200ICP_OK;
 }
 
 int b200icp_host_release(void) {

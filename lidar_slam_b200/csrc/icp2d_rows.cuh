@@ -435,7 +435,9 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
         for (int q = 0; q < R; ++q) {
           c[q] = -1;
           const float sval = __uint_as_float(second[q] & 0xffffffc0u);
-          amb[q] = !(sval > thr[q]);
+          // a second swept block within the slack makes the query ambiguous; no second block at all
+          // (every other block was pruned, or the target has one block) does not
+          amb[q] = second[q] != 0xffffffffu && !(sval > thr[q]);
           if (!amb[q]) {
             const int blk = (int)(best[q] & 63u);
             // groups of four targets whose minimum (kept from the sweep) is within the slack: all

@@ -461,6 +461,19 @@ __device__ __forceinline__ double warp_max_f64(double v) {
 }
 __device__ __forceinline__ double warp_min_f64(double v) { return -warp_max_f64(-v); }
 
+#ifdef B200ICP_FLOW_DEBUG
+#define FLOW_DBG(code) do { if (p.dist2_out && !p.nearest_only && threadIdx.x == 0) { \
+    volatile unsigned* dbg_ = reinterpret_cast<volatile unsigned*>(p.dist2_out); dbg_[64 + blockIdx.x] = (code); } } while (0)
+#define FLOW_DBG_W0(code) do { if (p.dist2_out && !p.nearest_only && threadIdx.x == 0) { \
+    volatile unsigned* dbg_ = reinterpret_cast<volatile unsigned*>(p.dist2_out); dbg_[64 + blockIdx.x] = (code); } } while (0)
+#define FLOW_CNT(i) do { if (p.dist2_out && !p.nearest_only && threadIdx.x == 0) \
+    atomicAdd_system(reinterpret_cast<unsigned*>(p.dist2_out) + (i), 1u); } while (0)
+#else
+#define FLOW_DBG(code) do { } while (0)
+#define FLOW_DBG_W0(code) do { } while (0)
+#define FLOW_CNT(i) do { } while (0)
+#endif
+
 template <bool PRUNE>
 __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const RunParams p, const FlowLayout L, char* ws) {
   __shared__ unsigned s_item;
@@ -477,6 +490,7 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
 
   for (;;) {
     // ---- pop a work item ----------------------------------------------------------------------
+    FLOW_DBG(1);
     if (tid == 0) {
       unsigned item = kRingEmpty;
       const unsigned ticket = atomicAdd(&ctl[kCtlHead], 1u);
@@ -498,6 +512,7 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
     __syncthreads();
     const unsigned item = s_item;
     if (item == kRingEmpty) break;
+    FLOW_DBG(2); FLOW_CNT(0);
     const int pair = (int)(item >> 21), chunk = (int)(item & 0x1fffffu);
     FlowPair* P = ps + pair;
     const int ns = P->ns, n_chunks = P->n_chunks;
@@ -721,8 +736,10 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
 #pragma unroll
       for (int k = 0; k < kRed3d; ++k) s_part[warp][k] = acc[k];
     }
+    FLOW_DBG(3);
     __syncthreads();
     if (warp != 0) continue;          // warps 1..7 wait for the next item at the barrier above
+    FLOW_DBG_W0(4);
 
     // ---- warp 0: this chunk's partial sums to global memory; retire the chunk -------------------
     const bool is_min = lane >= kSums3d && ((lane - kSums3d) & 1) == 0;
@@ -741,7 +758,9 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
     unsigned old = 0;
     if (lane == 0) old = atomicAdd(&P->done, 1u);
     old = __shfl_sync(full, old, 0);
+    FLOW_CNT(1);
     if (old != (unsigned)(n_chunks - 1)) continue;
+    FLOW_DBG_W0(5); FLOW_CNT(2);
 
     // ---- last chunk of the pass: totals in chunk order, solve, stop tests ------------------------
     __threadfence();
@@ -756,7 +775,12 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
     double tot[kRed3d];
 #pragma unroll
     for (int k = 0; k < kRed3d; ++k) tot[k] = __shfl_sync(full, v, k);
+    // every lane reads the pair's mutable state BEFORE lane 0 rewrites it below: without the barrier a
+    // lane that runs late would see the updated stop state, take the other branch and leave the warp
+    // waiting for it forever (seen at >= 24 chunks per pass)
     const int passes = __ldcg(&P->passes) + 1;
+    StopState st{__ldcg(&P->prev_err), __ldcg(&P->have_prev), __ldcg(&P->count)};
+    __syncwarp();
     double err = tot[15];
     if (normalize) {
       const double wx = tot[17] - tot[16], wy = tot[19] - tot[18], wz = tot[21] - tot[20];
@@ -793,12 +817,13 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
           nT[a * 4 + c] = Rm[a * 3] * T[c] + Rm[a * 3 + 1] * T[4 + c] + Rm[a * 3 + 2] * T[8 + c] + dt[a] * bottom[c];
 #pragma unroll
       for (int k = 0; k < 12; ++k) T[k] = nT[k];
-      StopState st{__ldcg(&P->prev_err), __ldcg(&P->have_prev), __ldcg(&P->count)};
       status = stop_test(st, err, P->epsilon, p.max_iters, p.stopping_thresh);
+      status = __shfl_sync(full, status, 0);          // one decision for the warp
       if (status < 0 && lane == 0) {
         P->prev_err = st.prev_err; P->have_prev = st.have_prev; P->count = st.count;
       }
     }
+    FLOW_DBG_W0(6);
     if (status < 0) {
       // ---- next pass: publish the pose, then the items -----------------------------------------
       if (lane == 0) {
@@ -809,20 +834,27 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
       }
       __threadfence();
       __syncwarp();
+      FLOW_DBG_W0(7);
       unsigned pos = 0;
       if (lane == 0) pos = atomicAdd(&ctl[kCtlTail], (unsigned)n_chunks);
+      FLOW_DBG_W0(70);
       pos = __shfl_sync(full, pos, 0);
+      FLOW_DBG_W0(71);
+#ifdef B200ICP_FLOW_DEBUG
+      if (p.dist2_out && lane == 0) { reinterpret_cast<volatile unsigned*>(p.dist2_out)[32] = pos; reinterpret_cast<volatile unsigned*>(p.dist2_out)[33] = (unsigned)n_chunks; reinterpret_cast<volatile unsigned*>(p.dist2_out)[34] = (unsigned)L.ring_cap; }
+#endif
+      // the ring never fills up (capacity 2x the items that can be in flight): every slot written here is empty
       for (int c = lane; c < n_chunks; c += 32) {
         unsigned* slot = ring + ((pos + (unsigned)c) & (unsigned)(L.ring_cap - 1));
         const unsigned it = ((unsigned)pair << 21) | (unsigned)c;
-        unsigned long long t0 = 0;
-        while (atomicCAS(slot, kRingEmpty, it) != kRingEmpty) {     // the ring never fills up (capacity 2x the items in flight)
-          if (ld_volatile_u32(&ctl[kCtlAbort]) != 0u) break;
-          __nanosleep(100);
-          if (t0 == 0) t0 = global_timer_ns();
-          else if (global_timer_ns() - t0 > kFlowSpinLimitNs) { atomicExch(&ctl[kCtlAbort], 1u); break; }
-        }
+        const unsigned was = atomicCAS(slot, kRingEmpty, it);
+#ifdef B200ICP_FLOW_DEBUG
+        if (p.dist2_out) reinterpret_cast<volatile unsigned*>(p.dist2_out)[128 + c] = was;
+#endif
+        if (was != kRingEmpty) atomicExch(&ctl[kCtlAbort], 2u);       // cannot happen; never spin on it
       }
+      FLOW_DBG_W0(72);
+      FLOW_DBG_W0(8); FLOW_CNT(3);
     } else {
       // ---- the pair is finished ------------------------------------------------------------------
       if (lane == 0) {
@@ -848,6 +880,7 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
       }
     }
   }
+  FLOW_DBG(9);
   if (lane == 0 && tiles)
     atomicAdd(reinterpret_cast<unsigned long long*>(ctl) + 1, (unsigned long long)tiles);
 }

@@ -104,7 +104,7 @@ __device__ __forceinline__ Ray make_ray(int sx, int sy, int ex, int ey, int widt
   // minor coordinate is monotone (non-strict) in k as well: bisect its entry and exit
   const int ms = r.steep ? sx : sy, me = r.steep ? ex : ey, mlim = r.steep ? width : height;
   auto minor = [&](int k) {
-    const int m = dx > 0 ? (int)(((unsigned)k * (unsigned)dy + (unsigned)r.c0) / (unsigned)dx) : 0;
+    const int m = dx > 0 ? (int)(((unsigned long long)k * (unsigned long long)dy + (unsigned long long)r.c0) / (unsigned long long)dx) : 0;   // 64-bit: k*dy wraps 32 bits for end points far outside a large grid
     return ms + (ms <= me ? m : -m);
   };
   // first k in [lo,hi] whose minor coordinate is within range, last such k
@@ -172,9 +172,9 @@ __device__ __forceinline__ void walk_ray(const Ray& r, int ray, int height, int3
   const int dx = r.dx, dy = r.dy;
   int m = 0, rem = r.c0;
   if (r.klo > 0) {
-    const unsigned num = (unsigned)r.klo * (unsigned)dy + (unsigned)r.c0;
-    m = (int)(num / (unsigned)dx);
-    rem = (int)(num - (unsigned)m * (unsigned)dx);
+    const unsigned long long num = (unsigned long long)r.klo * (unsigned long long)dy + (unsigned long long)r.c0;
+    m = (int)(num / (unsigned long long)dx);
+    rem = (int)(num - (unsigned long long)m * (unsigned long long)dx);
   }
   // the cell index advances by a fixed stride per major step and another per minor step
   const int smaj = r.steep ? (r.sy <= r.ey ? 1 : -1) : (r.sx <= r.ex ? height : -height);
@@ -217,7 +217,7 @@ __device__ __forceinline__ int ray_visit(const Ray& r, int cx, int cy) {
   if (r.klo > r.khi) return 0;
   const int k = r.steep ? (r.sy <= r.ey ? cy - r.sy : r.sy - cy) : (r.sx <= r.ex ? cx - r.sx : r.sx - cx);
   if (k < r.klo || k > r.khi) return 0;
-  const int m = r.dx > 0 ? (int)(((unsigned)k * (unsigned)r.dy + (unsigned)r.c0) / (unsigned)r.dx) : 0;
+  const int m = r.dx > 0 ? (int)(((unsigned long long)k * (unsigned long long)r.dy + (unsigned long long)r.c0) / (unsigned long long)r.dx) : 0;
   const int minor = r.steep ? r.sx + (r.sx <= r.ex ? m : -m) : r.sy + (r.sy <= r.ey ? m : -m);
   if (minor != (r.steep ? cx : cy)) return 0;
   return k == r.khi ? 1 : -1;

@@ -398,18 +398,72 @@ def shard_range(n_items: int, rank: int, world: int):
 
 
 _PEER_BUFFERS = {}
+_FLAG_WORDS = 16          # one uint32 arrival flag per rank (<= 16 ranks), per parity
+
+
+class PeerGather:
+    """Symmetric-memory gather buffer of the fused pose exchange, shared by all ranks of a group:
+    two row buffers [rows, 4] float64 used alternately (step parity) and one uint32 arrival flag per
+    rank and parity.  Every rank maps every other rank's copy, so a kernel stores rows -- and, when
+    its last pair retires, its flag -- straight into all of them over NVLink.  Protocol of step s
+    (parity p = s & 1, value s + 1), with NO host-side cross-rank barrier:
+      * the ICP launch stores this rank's rows into buffer p of every rank, then flag[p][rank] = s + 1;
+      * `wait()` (a stream-ordered kernel) returns once flag[p][r] >= s + 1 for every rank r: all rows
+        of step s are in this rank's buffer p;
+      * buffer p is written again in step s + 2, which a rank can only start after its wait of step
+        s + 1, i.e. after every rank has launched step s + 1, which in stream order comes after that
+        rank's consumers of step s: double buffering is what makes the pre-launch barrier unnecessary."""
+
+    def __init__(self, rows: int, dev, group):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        self.rows, self.dev = rows, dev
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        n_f64 = 2 * rows * 4 + 2 * _FLAG_WORDS // 2          # rows of both parities + 2 x 16 uint32 flags
+        self.buf = symm_mem.empty((n_f64,), dtype=torch.float64, device=dev)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, group=group if group is not None else dist.group.WORLD)
+        torch.cuda.synchronize(dev)
+        self.hdl.barrier(channel=0)                           # every rank's flags are zero before anyone stores
+        self.step = 0
+        self.timed_out = torch.zeros((1,), dtype=torch.int32, device=dev)
+        self.base_ptrs = [int(q) for q in self.hdl.buffer_ptrs]
+
+    def begin(self):
+        """(peer pointers of this step's row buffer, peer_flag triple, parity)"""
+        p = self.step & 1
+        ptrs = [b + p * self.rows * 32 for b in self.base_ptrs]
+        flag_off = (2 - p) * self.rows * 32 + p * 4 * _FLAG_WORDS
+        return ptrs, (flag_off, self.rank, self.step + 1), p
+
+    def rows_view(self, parity, rank=None):
+        """[rows, 4] view of this rank's (or a peer's) row buffer of the given parity."""
+        if rank is None or rank == self.rank:
+            return self.buf[parity * self.rows * 4:(parity + 1) * self.rows * 4].view(self.rows, 4)
+        whole = self.hdl.get_buffer(rank, (self.buf.numel(),), torch.float64)
+        return whole[parity * self.rows * 4:(parity + 1) * self.rows * 4].view(self.rows, 4)
+
+    def wait(self, parity):
+        """Stream-ordered: every rank's rows of the current step have landed in this rank's buffer."""
+        lib = _lib.load()
+        flags_ptr = self.buf.data_ptr() + 2 * self.rows * 32 + parity * 4 * _FLAG_WORDS
+        with torch.cuda.device(self.dev):
+            _lib.check(lib.b200icp_exchange_wait(ctypes.c_void_p(flags_ptr), self.world, self.step + 1, 20000,
+                                                 _ptr(self.timed_out), _stream_ptr()), "b200icp_exchange_wait")
+        self.step += 1
+        return self.rows_view(parity)
+
+    def check(self):
+        if int(self.timed_out.item()) != 0:
+            raise RuntimeError("fused pose exchange: a rank's arrival flag did not show up within 20 s")
 
 
 def _peer_gather_buffer(rows: int, dev, group):
-    """Symmetric-memory gather buffer [rows, 4] float64 shared by all ranks of `group` (cached):
-    every rank maps every other rank's copy, so a kernel can store straight into it over NVLink."""
-    import torch.distributed as dist
-    import torch.distributed._symmetric_memory as symm_mem
+    """Cached PeerGather for (rows, device, group)."""
     key = (rows, str(dev), id(group))
     if key not in _PEER_BUFFERS:
-        buf = symm_mem.empty((rows, 4), dtype=torch.float64, device=dev)
-        hdl = symm_mem.rendezvous(buf, group=group if group is not None else dist.group.WORLD)
-        _PEER_BUFFERS[key] = (buf, hdl)
+        _PEER_BUFFERS[key] = PeerGather(rows, dev, group)
     return _PEER_BUFFERS[key]
 
 
@@ -420,12 +474,13 @@ def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, exch
     Pairs are independent, so this is the only exchange.
 
     exchange="peer": fused -- the ICP kernel's epilogue stores each finished row directly into
-    every rank's symmetric-memory gather buffer (peer stores over NVLink / NVSwitch), followed by
-    one cross-rank barrier; no gather kernel, no collective.  exchange="nccl": pack_poses + ONE
-    all_gather_into_tensor (NCCL on GPUs, gloo in the CPU tests of the host logic).
-    "auto" = "peer" on CUDA with NCCL when symmetric memory is available, else "nccl".
+    every rank's symmetric-memory gather buffer (peer stores over NVLink / NVSwitch) and, when the
+    rank's last pair retires, an arrival flag; a stream-ordered wait on the flags of all ranks
+    follows.  No gather kernel, no collective, no host-side barrier (PeerGather).
+    exchange="nccl": pack_poses + ONE all_gather_into_tensor (NCCL on GPUs, gloo in the CPU tests of
+    the host logic).  "auto" = "peer" on CUDA with NCCL when symmetric memory is available, else "nccl".
     Returns (rows [B,4], local IcpBatchResult); with "peer" the rows alias the cached buffer and
-    are valid until the next sharded call of the same shape.
+    are valid until the sharded call after the next one of the same shape (two buffers alternate).
     """
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -439,23 +494,28 @@ def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, exch
         v = kw.get(key)
         if v is not None and not isinstance(v, (int, float, bool)):
             kw[key] = v[lo:hi]
-    use_peer = False
+    pg = None
     if world > 1 and exchange in ("auto", "peer") and torch.cuda.is_available() and dist.get_backend(group) == "nccl":
         try:
-            buf, hdl = _peer_gather_buffer(world * per, _device(), group)
-            use_peer = True
+            pg = _peer_gather_buffer(world * per, _device(), group)
         except Exception:                      # symmetric memory unavailable on this build / topology
             if exchange == "peer":
                 raise
-    if use_peer:
-        hdl.barrier(channel=0)                 # nobody still reads the previous contents
-        res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, peer_pose_ptrs=list(hdl.buffer_ptrs),
-                            peer_row0=rank * per, **kw)
-        if hi - lo < per:                      # this rank's padding rows, to every peer
+    if pg is not None:
+        ptrs, flag, parity = pg.begin()
+        if hi - lo < per:                      # this rank's padding rows, to every peer, ahead of the launch
             for r in range(world):
-                hdl.get_buffer(r, (world * per, 4), torch.float64)[rank * per + (hi - lo):(rank + 1) * per] = float("nan")
-        hdl.barrier(channel=1)                 # every rank's rows have landed everywhere
-        return buf[:n], res
+                pg.rows_view(parity, r)[rank * per + (hi - lo):(rank + 1) * per] = float("nan")
+        if hi > lo:
+            res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, peer_pose_ptrs=ptrs, peer_row0=rank * per,
+                                peer_flag=flag, **kw)
+        else:                                  # an empty shard still announces itself
+            res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, **kw)
+            ex, keep = _lib.make_exchange(ptrs, rank * per, *flag)
+            with torch.cuda.device(pg.dev):
+                _lib.check(_lib.load().b200icp_exchange_signal(ctypes.byref(ex), _stream_ptr()), "b200icp_exchange_signal")
+        rows = pg.wait(parity)
+        return rows[:n], res
     res = run_icp_batch(scans, counts, pairs_t[lo:hi], init_loc, **kw)
     local = torch.full((per, 4), float("nan"), dtype=torch.float64, device=res.T.device)
     if hi > lo:

@@ -98,6 +98,22 @@ def run_icp_batch_host(scans: np.ndarray, counts: np.ndarray, pairs: np.ndarray,
     return HostBatchResult(T, err, iters, status, corr)
 
 
+def run_icp_pair_host(src: np.ndarray, tgt: np.ndarray, init: np.ndarray, epsilon: float, max_iters: int,
+                      stopping_thresh: float, normalize: bool, want_corr: bool):
+    """ONE pair through b200icp_run_pair_host (the C form of the reference's run_icp call): contiguous
+    float64 (n, dim) clouds of one dimension, init (4, 4).  Returns (T, error, passes, status, corr|None)."""
+    lib = _lib.load()
+    T = np.empty((4, 4), dtype=np.float64)
+    err = np.empty((1,), dtype=np.float64)
+    meta = np.empty((2,), dtype=np.int32)
+    corr = np.empty((src.shape[0],), dtype=np.int32) if want_corr else None
+    _lib.check(lib.b200icp_run_pair_host(_p(src), src.shape[0], _p(tgt), tgt.shape[0], src.shape[1], _p(init),
+                                         float(epsilon), int(max_iters), float(stopping_thresh), 1 if normalize else 0,
+                                         _p(T), _p(err), ctypes.c_void_p(meta.ctypes.data),
+                                         ctypes.c_void_p(meta.ctypes.data + 4), _p(corr)), "b200icp_run_pair_host")
+    return T, err[0], int(meta[0]), int(meta[1]), corr
+
+
 def beam_tables(n_beams: int):
     """cos / sin of linspace(-135 deg, +135 deg, n_beams) exactly as the reference evaluates them
     (modules/localization.py:273-278), numpy on the host."""

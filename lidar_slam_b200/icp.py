@@ -5,25 +5,26 @@ conventions, computed by the B200 engine.
     import lidar_slam_b200.icp as icp          # or install(), see INTEGRATION.md
     T = icp.run_icp(z[i], z[i-1], init_transform=T0, epsilon=0.001)
 
-Every call is a batch of one through the same kernels `run_icp_batch` uses, and
-synchronises before returning numpy, like the synchronous reference.
+Every call is a batch of one through the same kernels `run_icp_batch` uses
+(`b200icp_run_pair_host`: one pinned staging block, one copy up, one launch with a
+latency-oriented CTA shape, one copy back; no torch on the path), and is synchronous
+like the reference.
 """
 from __future__ import annotations
 
 import sys
 
 import numpy as np
-import torch
 
-from . import engine
+from . import hostapi
 
 __all__ = ["run_icp", "voxel_downsample", "install"]
 
 
 def _cloud(pc, name):
-    if isinstance(pc, torch.Tensor):
+    if hasattr(pc, "detach"):                 # torch tensors are accepted as an extension
         pc = pc.detach().cpu().numpy()
-    pc = np.asarray(pc, dtype=np.float64)
+    pc = np.ascontiguousarray(pc, dtype=np.float64)
     if pc.ndim != 2 or pc.shape[1] not in (2, 3):
         raise ValueError(f"{name} must have shape (N,2) or (N,3), got {pc.shape}")
     if pc.shape[0] == 0:
@@ -50,21 +51,17 @@ def run_icp(
     """
     src, tgt = _cloud(pc1, "pc1"), _cloud(pc2, "pc2")
     if src.shape[1] != tgt.shape[1]:      # the reference pads 2-D clouds with z = 0 (icp.py:153-156)
-        pad = lambda c: c if c.shape[1] == 3 else np.concatenate([c, np.zeros((c.shape[0], 1))], axis=1)
+        pad = lambda c: c if c.shape[1] == 3 else np.ascontiguousarray(np.concatenate([c, np.zeros((c.shape[0], 1))], axis=1))
         src, tgt = pad(src), pad(tgt)
-    init = np.asarray(init_transform, dtype=np.float64)
+    init = np.ascontiguousarray(init_transform, dtype=np.float64)
     if init.shape != (4, 4):
         raise ValueError("init_transform must be 4x4")
-    scans, counts = engine.pack_scans([src, tgt])
-    res = engine.run_icp_batch(
-        scans, counts, np.array([[0, 1]], dtype=np.int32), init[None], epsilon=float(epsilon),
-        max_iters=int(max_iters), stopping_thresh=float(stopping_thresh),
-        normalize_error=bool(normalize_error), return_correspondences=bool(return_correspondences))
-    T = res.T[0].cpu().numpy()
-    if return_error:
-        error = np.float64(res.error[0].item())
+    T, error, _, _, corr32 = hostapi.run_icp_pair_host(src, tgt, init, float(epsilon), int(max_iters),
+                                                       float(stopping_thresh), bool(normalize_error),
+                                                       bool(return_correspondences))
+    error = np.float64(error)
     if return_correspondences:
-        corr = res.corr[0, :src.shape[0]].cpu().numpy().astype(np.int64)
+        corr = corr32.astype(np.int64)
     if return_error and not return_correspondences:
         return T, error
     if return_correspondences and not return_error:
@@ -77,6 +74,8 @@ def run_icp(
 def voxel_downsample(point_cloud, voxel_size):
     """Signature and semantics of modules/icp.py:4-27 (per-voxel mean, voxels in
     lexicographic index order), computed on the device."""
+    import torch
+    from . import engine
     pts = _cloud(point_cloud, "point_cloud")
     if pts.shape[1] != 3:
         pts3 = np.concatenate([pts, np.zeros((pts.shape[0], 1))], axis=1)

@@ -212,6 +212,58 @@ def thin_scans(scans, counts, seed, lo=100, hi=N_BEAMS):
     return scans, counts
 
 
+def thin_scans_fast(scans, counts, seed, lo=100):
+    """Vectorised thin_scans (its own random stream): every scan keeps a uniformly drawn number of
+    beams in [min(lo, n), n], chosen uniformly, beam order kept.  numpy in, numpy out."""
+    scans = np.asarray(scans)
+    counts = np.asarray(counts).astype(np.int64)
+    S, N = scans.shape[0], scans.shape[1]
+    rng = np.random.default_rng(seed)
+    lo_i = np.minimum(lo, counts)
+    keep_n = lo_i + np.floor(rng.random(S) * (counts - lo_i + 1)).astype(np.int64)
+    keep_n = np.minimum(keep_n, counts)
+    keys = rng.random((S, N))
+    keys[np.arange(N)[None, :] >= counts[:, None]] = 2.0            # not a beam
+    rank = np.argsort(np.argsort(keys, axis=1, kind="stable"), axis=1, kind="stable")
+    keep = rank < keep_n[:, None]
+    order = np.argsort(~keep, axis=1, kind="stable")               # kept beams first, beam order preserved
+    out = np.take_along_axis(scans, order[:, :, None], axis=1)
+    out[np.arange(N)[None, :] >= keep_n[:, None]] = 0.0
+    return out, keep_n.astype(np.int32)
+
+
+def gtsam_batch(n_pairs=4955, fixed_interval=10, seed=20, device="cpu"):
+    """Config-3 shaped workload (`main.py --mode gtsam --filter_lidar --fixed_interval 10`): ragged
+    filtered scans; the consecutive-scan pairs (odometry init, epsilon 1e-3, raw SSE;
+    localization.py:112-123) followed by the loop-closure pairs (i, i + k), i = 0, k, 2k, ... with
+    identity init, epsilon 1e-2 and normalised error (main.py:161-172), as ONE pair list.
+    Returns dict(scans, counts, pairs, init, epsilon, normalize, n_odometry)."""
+    b = odometry_batch(n_pairs, seed=seed, device=device, n_traj=1)       # ray casting where the caller computes
+    scans, counts = thin_scans_fast(b["scans"].cpu().numpy(), b["counts"].cpu().numpy(), seed + 5)
+    loop_src = np.arange(0, n_pairs + 1 - fixed_interval, fixed_interval)
+    pairs = np.concatenate([b["pairs"].cpu().numpy(), np.stack([loop_src, loop_src + fixed_interval], axis=1).astype(np.int32)])
+    init = np.concatenate([b["init"].cpu().numpy(), np.tile(np.eye(4), (len(loop_src), 1, 1))])
+    eps = np.concatenate([np.full(n_pairs, 1e-3), np.full(len(loop_src), 1e-2)])
+    norm = np.concatenate([np.zeros(n_pairs, np.uint8), np.ones(len(loop_src), np.uint8)])
+    to = lambda x: torch.as_tensor(x).to(device)
+    return {"scans": to(scans), "counts": to(counts), "pairs": to(pairs), "init": to(init), "epsilon": to(eps),
+            "normalize": to(norm), "n_odometry": n_pairs}
+
+
+def yaw_sweep_batch(n_source, n_targets=4, n_yaw=24, seed=1, kind="drill"):
+    """Configs 1 / 4 (code/icp_warm_up/test_icp.py:61-91): one canonical model, n_targets partial views,
+    n_yaw yaw initialisations per view with centroid-aligned translation.  numpy arrays:
+    dict(clouds [source, targets...], pairs [n_targets*n_yaw, 2], init [.., 4, 4])."""
+    src = drill_cloud(n_source, seed=seed) if kind == "drill" else container_cloud(n_source, seed=seed)
+    tgts = [partial_view(src, seed=10 * seed + k) for k in range(n_targets)]
+    pairs, inits = [], []
+    for j, t in enumerate(tgts):
+        for T0 in yaw_sweep_inits(src, t, n_yaw):
+            pairs.append((0, 1 + j))
+            inits.append(T0)
+    return {"clouds": [src] + tgts, "pairs": np.array(pairs, np.int32), "init": np.stack(inits)}
+
+
 # --------------------------------------------------------------------------
 # 3-D objects
 # --------------------------------------------------------------------------

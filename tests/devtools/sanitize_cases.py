@@ -1,4 +1,5 @@
-"""Tiny run of every kernel for compute-sanitizer (memcheck):  compute-sanitizer --tool memcheck python tests/devtools/sanitize_cases.py"""
+"""Tiny run of every kernel for compute-sanitizer, ONE tool per gpurun call (memcheck, racecheck, synccheck):
+   compute-sanitizer --tool memcheck python tests/devtools/sanitize_cases.py   -> profiles/r2_sanitizer_*.txt"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
@@ -30,5 +31,25 @@ disp, rgb = to.synthetic_frames(2, 120, 160, seed=5)
 p = tm.TexturePainter(81, 61, 0.1, -4.0, -3.0, to.T_RC, to.K)
 p.paint_frames(disp, rgb, poses[:2])
 p.resolve(m.grid_map[:81, :61].copy())
+# gated host entries: two slices, sorted and reversed pair lists; ranges in; the single-pair entry
+from lidar_slam_b200 import hostapi, _lib
+g = synth.odometry_batch(40, seed=6, device="cuda", with_ranges=True)
+h = {k: g[k].cpu().numpy() for k in ("scans", "counts", "pairs", "init", "ranges")}
+for pr, ini in ((h["pairs"], h["init"]), (h["pairs"][::-1].copy(), h["init"][::-1].copy())):
+    hostapi.run_icp_batch_host(h["scans"], h["counts"], pr, ini, epsilon=1e-3, flags=_lib.flag_slices(2),
+                               return_correspondences=True)
+    hostapi.run_icp_ranges_host(h["ranges"], pr, ini, epsilon=1e-3, flags=_lib.flag_slices(2))
+engine.run_icp_ranges_batch(g["ranges"], g["pairs"], g["init"], epsilon=1e-3, return_correspondences=True)
+eng.run_icp(h["scans"][1, :h["counts"][1]], h["scans"][0, :h["counts"][0]], init_transform=h["init"][0], epsilon=1e-3,
+            return_error=True, return_correspondences=True)
+eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, flags=engine.FLAG_EXHAUSTIVE)
+eng.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, flags=engine.FLAG_NO_PRUNE)
+# the general kernel with several chunks per pass and shared targets
+src2 = synth.drill_cloud(2600, seed=4)
+tg2 = [synth.partial_view(src2, seed=20 + k) for k in range(2)]
+pool2, counts2 = eng.pack_scans([src2] + tg2)
+prs2 = torch.tensor([(0, 1), (0, 2), (0, 1), (0, 2)], dtype=torch.int32).cuda()
+ini2 = torch.tensor(np.stack([synth.yaw_sweep_inits(src2, tg2[0], 24)[k] for k in (0, 3, 7, 11)])).cuda()
+eng.run_icp_batch(pool2, counts2, prs2, ini2, epsilon=1e-3, normalize_error=True, return_correspondences=True)
 torch.cuda.synchronize()
 print("sanitize cases done")

@@ -16,6 +16,11 @@ import types
 
 import numpy as np
 
+# The reference updates a float32 grid with `grid[idx] -= np.float64(...)`: under NumPy >= 2 (NEP 50)
+# that is f32(f64(cell) - log 4), which is what csrc/ogm.cu reproduces; NumPy 1.x value-based casting would
+# evaluate it in float32.  The fixtures are therefore tied to the NumPy major version that made them.
+assert int(np.__version__.split('.')[0]) >= 2, 'regenerate the ogm goldens under NumPy >= 2 (NEP 50 promotion)'
+
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)

@@ -27,7 +27,24 @@ WORKER = textwrap.dedent("""
     full = engine.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3)
     assert torch.equal(p, engine.pack_poses(full.T, full.error))
     p2, _ = engine.run_icp_sharded(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, exchange="peer")
-    assert torch.equal(p2, a)                                    # buffer reuse across calls
+    assert torch.equal(p2, a)                                    # the other row buffer (parity 1)
+    assert torch.equal(p, a)                                     # ... and the first one is still intact
+    for step in range(5):                                        # buffers and arrival flags reused, no barrier between
+        c = synth.odometry_batch(23 + step, seed=30 + step, device="cuda")
+        want, _ = engine.run_icp_sharded(c["scans"], c["counts"], c["pairs"], c["init"], epsilon=1e-3, exchange="nccl")
+        got, _ = engine.run_icp_sharded(c["scans"], c["counts"], c["pairs"], c["init"], epsilon=1e-3, exchange="peer")
+        assert torch.equal(got, want), step
+    for pg in engine._PEER_BUFFERS.values():
+        pg.check()
+    # the general (3-D) kernel has the same epilogue
+    import numpy as np
+    src = synth.drill_cloud(900, seed=1); tgt = synth.partial_view(src, seed=2)
+    pool, counts = engine.pack_scans([src, tgt])
+    inits = torch.tensor(np.stack(synth.yaw_sweep_inits(src, tgt, 24)[:7])).cuda()
+    prs = torch.tensor([[0, 1]] * 7, dtype=torch.int32).cuda()
+    want, _ = engine.run_icp_sharded(pool, counts, prs, inits, epsilon=1e-3, normalize_error=True, exchange="nccl")
+    got, _ = engine.run_icp_sharded(pool, counts, prs, inits, epsilon=1e-3, normalize_error=True, exchange="peer")
+    assert torch.equal(got, want)
     dist.barrier(); dist.destroy_process_group()
     print("rank", rank, "ok")
 """) % ROOT
