@@ -148,7 +148,9 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
   if (cudaMemsetAsync(workspace, 0, 256, stream) != cudaSuccess) return B200ICP_ERR_CUDA;
   if (dim == 2 && p.n_max <= kMax2d) {
     if (!(flags & B200ICP_FLAG_EXHAUSTIVE) || p.ranges) {
-      // row kernel: rows of 32*R source points per warp step; capacity is not a function of W
+      // row kernel: rows of 32*R source points per warp step; capacity is not a function of W.
+      // R = 1 (one query per lane): tighter row boxes, fewer candidate blocks swept than R = 2..4
+      // (profiles/r2l_row_kernel_cta_shapes.txt: 1.77 ms vs 1.98 ms per 4941-pair step)
       if (p.n_max <= 512) return launch_rows<4, 1, 5>(p, stream, d.sms, flags);
       if (p.n_max <= 1280) {
 #ifdef B200ICP_TUNE_VARIANTS
@@ -164,10 +166,10 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
         }
 #endif
         // few pairs (the un-batched drop-in): 16 warps on each pair, 1-2 rows per warp and pass
-        if ((flags & B200ICP_FLAG_LATENCY) && p.n_pairs <= d.sms) return launch_rows<16, 2, 1>(p, stream, d.sms, flags);
-        return launch_rows<4, 2, 4>(p, stream, d.sms, flags);
+        if ((flags & B200ICP_FLAG_LATENCY) && p.n_pairs <= d.sms) return launch_rows<16, 1, 1>(p, stream, d.sms, flags);
+        return launch_rows<4, 1, 4>(p, stream, d.sms, flags);
       }
-      return launch_rows<8, 2, 2>(p, stream, d.sms, flags);
+      return launch_rows<8, 1, 2>(p, stream, d.sms, flags);
     }
     // exhaustive register-tiled kernel (round 1): W warps, up to R rows of 32 source points per
     // warp: capacity 32*R*W >= n_max; 80 registers, 3 CTAs/SM at 1081 points (FMA-bound)
