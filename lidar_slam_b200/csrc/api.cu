@@ -150,18 +150,21 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
     if (!(flags & B200ICP_FLAG_EXHAUSTIVE) || p.ranges) {
       // row kernel: rows of 32*R source points per warp step; capacity is not a function of W.
       // R = 1 (one query per lane): tighter row boxes, fewer candidate blocks swept than R = 2..4
-      // (profiles/r2l_row_kernel_cta_shapes.txt: 1.77 ms vs 1.98 ms per 4941-pair step)
+      // (profiles/r2_row_kernel_cta_shapes.txt: 1.77 ms vs 1.98 ms per 4941-pair step)
       if (p.n_max <= 512) return launch_rows<4, 1, 5>(p, stream, d.sms, flags);
       if (p.n_max <= 1280) {
 #ifdef B200ICP_TUNE_VARIANTS
-        // developer build: CTA shapes for A/B timing, selected by flags bits 24..27
-        switch ((flags >> 24) & 0xfu) {
-          case 1: return launch_rows_variant<6, 2, 4, true, false>(p, stream, d.sms);
-          case 2: return launch_rows_variant<8, 2, 3, true, false>(p, stream, d.sms);
-          case 3: return launch_rows_variant<4, 1, 4, true, false>(p, stream, d.sms);
-          case 4: return launch_rows_variant<8, 1, 4, true, false>(p, stream, d.sms);
-          case 5: return launch_rows_variant<5, 2, 4, true, false>(p, stream, d.sms);
-          case 6: return launch_rows_variant<3, 2, 4, true, false>(p, stream, d.sms);
+        // developer build: CTA shapes for A/B timing, selected by the environment at every call
+        // (tests/devtools/time_variants.py)
+        if (const char* e = getenv("B200ICP_VARIANT")) switch (atoi(e)) {
+          case 1: return launch_rows_variant<4, 2, 4, true, false>(p, stream, d.sms);
+          case 2: return launch_rows_variant<8, 2, 2, true, false>(p, stream, d.sms);
+          case 3: return launch_rows_variant<6, 1, 3, true, false>(p, stream, d.sms);
+          case 4: return launch_rows_variant<8, 1, 2, true, false>(p, stream, d.sms);
+          case 5: return launch_rows_variant<5, 1, 3, true, false>(p, stream, d.sms);
+          case 6: return launch_rows_variant<3, 1, 5, true, false>(p, stream, d.sms);
+          case 7: return launch_rows_variant<4, 3, 4, true, false>(p, stream, d.sms);
+          case 8: return launch_rows_variant<2, 1, 8, true, false>(p, stream, d.sms);
           default: break;
         }
 #endif

@@ -9,9 +9,10 @@
 // What changed against icp2d.cuh (round 1, kept as the exhaustive register-tiled variant): the
 // profile of that kernel showed 23 % of its issue slots in the candidate arithmetic and 77 % in
 // per-row fixed work (address arithmetic, 64-bit mask loops, spills, predicates for the ragged
-// tail, reductions).  Here a warp walks ROWS of 32*R consecutive source points (R = 2: two queries
-// per lane, 32 apart), so that every warp-level step -- row box, block bounds, seeds, ballots, the
-// shared-memory loads of a target block -- is paid once per 64 queries; ragged tails are clamped
+// tail, reductions).  Here a warp walks ROWS of 32*R consecutive source points (R queries per lane,
+// 32 apart; R = 1 ships: R = 2..4 pay every warp-level step -- row box, block bounds, seeds,
+// ballots, the shared-memory loads of a target block -- once per 64..128 queries but their wider
+// row boxes admit more blocks, measured slower; api.cu); ragged tails are clamped
 // duplicates instead of predicates; target blocks beyond the scan are +inf boxes instead of
 // tests; matches live in a 2-byte shared array instead of a register queue; the bounding box of
 // the normalised error is a separate light pass that only normalised pairs execute.

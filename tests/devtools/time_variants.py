@@ -1,6 +1,6 @@
-"""Developer A/B of CTA shapes of the planar row kernel (library built with -DB200ICP_TUNE_VARIANTS):
-   B200ICP_NVCC_EXTRA=-DB200ICP_TUNE_VARIANTS python -m lidar_slam_b200.build --force
-   python tests/devtools/time_variants.py [n_pairs]"""
+"""Developer A/B of CTA shapes of the planar row kernel.  Needs a library built with
+-DB200ICP_TUNE_VARIANTS (tools/gpu/build_tune_lib.sh writes tests/devtools/_tune/libb200icp_tune.so):
+   B200ICP_LIB=tests/devtools/_tune/libb200icp_tune.so python tests/devtools/time_variants.py [n_pairs]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
@@ -8,7 +8,8 @@ from lidar_slam_b200 import engine, synth
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4955
 pools = [synth.odometry_batch(n, seed=20 + 10 * k, device="cuda", n_traj=1) for k in range(2)]
-names = {0: "W4 R2 (default)", 1: "W6 R2", 2: "W8 R2 minb3", 3: "W4 R1", 4: "W8 R1", 5: "W5 R2", 6: "W3 R2"}
+names = {0: "W4 R1 minb4 (default)", 1: "W4 R2 minb4", 2: "W8 R2 minb2", 3: "W6 R1 minb3", 4: "W8 R1 minb2",
+         5: "W5 R1 minb3", 6: "W3 R1 minb5", 7: "W4 R3 minb4", 8: "W2 R1 minb8"}
 ref = None
 for rep in range(2):
     for v, name in names.items():
@@ -17,8 +18,8 @@ for rep in range(2):
             b = pools[k % 2]
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
-            r = engine.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, planar_fallback=False,
-                                     flags=v << 24)
+            os.environ["B200ICP_VARIANT"] = str(v)
+            r = engine.run_icp_batch(b["scans"], b["counts"], b["pairs"], b["init"], epsilon=1e-3, planar_fallback=False)
             e.record(); e.synchronize()
             if k >= 2:
                 ms.append(s.elapsed_time(e))
