@@ -33,6 +33,8 @@ extern "C" {
 #define B200ICP_ERR_WORKSPACE (-3) /* workspace smaller than b200icp_workspace_bytes  */
 #define B200ICP_ERR_CUDA (-4)      /* launch failed; see cudaGetLastError             */
 #define B200ICP_ERR_NO_DEVICE (-5) /* no sm_100 device / wrong architecture           */
+#define B200ICP_ERR_STATIC_SCRATCH (-6) /* b200icp_run_static: the problem needs more scratch than
+                                           B200ICP_STATIC_SCRATCH_BYTES; use b200icp_run       */
 
 /* ---- per-pair status (status_out) --------------------------------------------
  * Which of the reference's three stop tests fired (modules/icp.py:172-178), or
@@ -274,6 +276,29 @@ int b200icp_run_pair_host(const double* src, int n_src, const double* tgt, int n
                           int normalize, double* T_out, double* err_out, int32_t* iters_out,
                           int32_t* status_out, int32_t* corr_out);
 int b200icp_host_release(void);
+
+/* b200icp_run without a workspace argument, for callers that cannot allocate device memory at all
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE: this entry was added.
+ * Same arguments, outputs and results as b200icp_run (bit for bit: the same kernels run), but the
+ * scratch memory (work queue; for the general kernel also the per-pair state, the work-item ring, the
+ * partial sums and the Morton-sorted copies of the referenced scans) lives in ONE fixed array of
+ * B200ICP_STATIC_SCRATCH_BYTES inside the library's device image: every GPU that loads the library
+ * holds that much memory until the process exits.  The entry calls no cudaMalloc / cudaFree / any
+ * allocating routine.  A problem whose b200icp_workspace_bytes(n_pairs, n_max, dim) exceeds
+ * B200ICP_STATIC_SCRATCH_BYTES is rejected with B200ICP_ERR_STATIC_SCRATCH before anything is launched
+ * (the planar kernel, dim 2 and n_max <= 2048, needs 256 bytes for any number of pairs; the general
+ * kernel needs about 100 bytes per point of every referenced scan, e.g. 24 pairs of 3000-point
+ * clouds = 7 MiB).  The array is SHARED by every call on a device and keeps the last call's contents
+ * (each call re-initialises the words it needs at zero, on the given stream): two calls that overlap
+ * on the GPU -- different streams, or different host threads -- RACE on it; serialise them on one
+ * stream or use b200icp_run with separate workspaces. */
+#define B200ICP_STATIC_SCRATCH_BYTES (16u << 20)
+int b200icp_run_static(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                       const int32_t* pairs, const double* init, const double* epsilon,
+                       const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                       double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                       int32_t* corr_out, void* stream);
 
 /* One exact nearest-neighbour pass, exposed on its own for tests and for the
  * roofline measurement.  Replaces get_correspondences / KDTree.query

@@ -21,6 +21,9 @@ SIGNATURES = {
     "b200icp_run": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200icp_run_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p]),
     "b200icp_run_exchange": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_int,
@@ -74,6 +77,8 @@ SIGNATURES = {
 }
 
 # launch flags (include/b200icp.h)
+STATIC_SCRATCH_BYTES = 16 << 20      # B200ICP_STATIC_SCRATCH_BYTES (b200icp_run_static)
+ERR_STATIC_SCRATCH = -6
 FLAG_EXHAUSTIVE = 0x1
 FLAG_HOST_CHUNKED = 0x2
 FLAG_NO_PRUNE = 0x4

@@ -246,6 +246,9 @@ const char* b200icp_error_string(int code) {
     case B200ICP_ERR_WORKSPACE: return "workspace missing or smaller than b200icp_workspace_bytes";
     case B200ICP_ERR_CUDA: return "CUDA launch failed";
     case B200ICP_ERR_NO_DEVICE: return "no sm_100 (B200) device is current";
+    case B200ICP_ERR_STATIC_SCRATCH:
+      return "b200icp_run_static: problem needs more scratch than B200ICP_STATIC_SCRATCH_BYTES (16 MiB); "
+             "use b200icp_run with a caller workspace";
     default: return "unknown error code";
   }
 }
@@ -410,3 +413,59 @@ int b200icp_ffma_probe(float* sink, int n_blocks, int iters, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// b200icp_run_static: b200icp_run with its scratch in the library's device image (no allocation
+// anywhere on the call path).  No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (graph capture, serving loops).
+//
+// In host code `g_static_scratch` is only a host-side stand-in for the device array: its device
+// address is looked up once per device with cudaGetSymbolAddress (with that device current) and
+// that pointer is what the kernels get.  Every call on a device shares the array; calls that
+// overlap on the GPU race (include/b200icp.h).
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_static_scratch[B200ICP_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+void* g_static_ptr[kStaticMaxDevices];        // device address of g_static_scratch, per device ordinal
+
+int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices) return B200ICP_ERR_NO_DEVICE;
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_ptr[dev]) {
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess || !ptr) {
+      (void)cudaGetLastError();
+      return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? B200ICP_ERR_NO_DEVICE : B200ICP_ERR_CUDA;
+    }
+    g_static_ptr[dev] = ptr;
+  }
+  *out = g_static_ptr[dev];
+  return B200ICP_OK;
+}
+}  // namespace
+
+extern "C" int b200icp_run_static(const double* scans, const int32_t* counts, int n_scans, int n_max, int dim,
+                                  const int32_t* pairs, const double* init, const double* epsilon,
+                                  const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                                  double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                                  int32_t* corr_out, void* stream) {
+  size_t need = 0;
+  const int rc = b200icp_workspace_bytes(n_pairs, n_max, dim, &need);
+  if (rc != B200ICP_OK) return rc;
+  if (need > (size_t)B200ICP_STATIC_SCRATCH_BYTES) return B200ICP_ERR_STATIC_SCRATCH;
+  void* scratch = nullptr;
+  const int rs = static_scratch_for_current_device(&scratch);
+  if (rs != B200ICP_OK) return rs;
+  // dispatch() clears the control block (first 256 bytes) on `stream`; the setup kernel of the general
+  // path rewrites ring, per-pair state and slot headers, so nothing else has to start at zero.
+  return run_common(scans, counts, n_scans, n_max, dim, pairs, init, epsilon, normalize, n_pairs, max_iters,
+                    stopping_thresh, T_out, err_out, iters_out, status_out, corr_out, scratch,
+                    (size_t)B200ICP_STATIC_SCRATCH_BYTES, stream, nullptr);
+}
