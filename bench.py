@@ -622,6 +622,34 @@ def run_b200_arm(args):
     if not (torch.allclose(exh_res.T, same.T, rtol=1e-11, atol=1e-11) and torch.equal(exh_res.iters, same.iters)
             and torch.allclose(exh_res.error, same.error, rtol=1e-11, atol=0)):
         raise RuntimeError("row kernel and exhaustive kernel disagree on the bench batch")
+    # two batches in flight (world 1 only; the exchange protocol is stream-ordered): launches alternate on
+    # two streams, so the head of step k + 1 fills the SMs the queue tail of step k leaves idle -- what a
+    # caller with several batches does.  Reported beside `value`, which stays one launch after the other.
+    two_stream_ms = None
+    if world == 1:
+        cur = torch.cuda.current_stream()
+        lanes = [torch.cuda.Stream(), torch.cuda.Stream()]
+        keep = []
+        for rep in range(2):                      # first repetition warms the second stream's allocations
+            torch.cuda.synchronize()
+            ev0.record()
+            for ln in lanes:
+                ln.wait_stream(cur)
+            for k in range(args.steps):
+                with torch.cuda.stream(lanes[k % 2]):
+                    keep.append(step_device(k)[0])
+                if len(keep) > 4:
+                    keep.pop(0)
+            for ln in lanes:
+                cur.wait_stream(ln)
+            ev1.record()
+            torch.cuda.synchronize()
+            two_stream_ms = ev0.elapsed_time(ev1)
+        pipelined = keep[-1]
+        want = results[(args.steps - 1) % N_POOLS]
+        if not (torch.equal(pipelined.T, want.T) and torch.equal(pipelined.iters, want.iters)):
+            raise RuntimeError("two launches in flight changed a result")
+        del keep
     clocks = sampler.stop(t_wall0, time.perf_counter()) if rank == 0 else None
 
     # ---- timed region 2: end to end through the C ABI's host entry ----
@@ -729,6 +757,12 @@ def run_b200_arm(args):
         "dropin_ms_per_call": dropin_ms,
         "clocks": clocks,
     }
+    if two_stream_ms is not None:
+        line["two_stream_value"] = {
+            "value": B * args.steps / (two_stream_ms * 1e-3), "unit": UNIT, "ms_per_step": two_stream_ms / args.steps,
+            "note": "same steps with launches alternating on two streams (two batches in flight): the head of step k + 1 "
+                    "fills the SMs the queue tail of step k leaves idle; results identical; `value` itself is one launch "
+                    "after the other"}
     if arm is not None and world == 1:
         n_sample = min(B, _cpu_sample_size())
         staged = arm.stage(_sample_from_batch(pools[0], np.arange(n_sample)))

@@ -79,13 +79,15 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
 // factor 2 to spare.  A candidate set {t : d32(t) <= m + 2*slack} around the
 // fp32 minimum m therefore always contains the float64 nearest neighbour; the
 // callers use 4*slack (and evaluate at an upper bound of m).
-// tests/test_host.py::test_fp32_slack_bounds_the_float64_distance checks the inequality on adversarial inputs
-// (tests/test_margin.py adds near-ties, large offsets and denormals).
+// tests/test_host.py::test_fp32_slack_bounds_the_fp64_distance checks the inequality on random clouds,
+// tests/test_margin.py on near-ties, offsets of kilometres, subnormal separations and fp32 collisions.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ float slack(float d_hi, float a_bound) {
   float s = sqrtf(d_hi);
   float as = a_bound + s;
-  return 8.0f * kU * as * s + 8.0f * kU * d_hi + 8.0f * kU * kU * as * as;
+  // + FLT_MIN: where the squares are subnormal in fp32 (separations below ~1e-19) the relative bound
+  // underflows to 0 while every product still errs by up to 2^-150 (tests/test_margin.py)
+  return 8.0f * kU * as * s + 8.0f * kU * d_hi + 8.0f * kU * kU * as * as + 1.1754944e-38f;
 }
 
 // Upper bound of the true block minimum given the truncated packed value

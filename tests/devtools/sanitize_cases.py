@@ -51,5 +51,18 @@ pool2, counts2 = eng.pack_scans([src2] + tg2)
 prs2 = torch.tensor([(0, 1), (0, 2), (0, 1), (0, 2)], dtype=torch.int32).cuda()
 ini2 = torch.tensor(np.stack([synth.yaw_sweep_inits(src2, tg2[0], 24)[k] for k in (0, 3, 7, 11)])).cuda()
 eng.run_icp_batch(pool2, counts2, prs2, ini2, epsilon=1e-3, normalize_error=True, return_correspondences=True)
+# the allocation-free entry (scratch in the library's device image), general and planar kernel
+import ctypes
+lib = _lib.load()
+vp = lambda t: ctypes.c_void_p(t.data_ptr())
+for pool_t, counts_t, pairs_t, init_t, dim in ((pool2, counts2, prs2, ini2, 3), (b["scans"], b["counts"], b["pairs"], b["init"], 2)):
+    n = int(pairs_t.shape[0])
+    pairs_t = pairs_t.to("cuda", torch.int32).contiguous(); init_t = init_t.to("cuda", torch.float64).contiguous()
+    eps_t = torch.full((n,), 1e-3, dtype=torch.float64, device="cuda"); nz = torch.zeros((n,), dtype=torch.uint8, device="cuda")
+    T = torch.empty((n, 4, 4), dtype=torch.float64, device="cuda"); er = torch.empty((n,), dtype=torch.float64, device="cuda")
+    it = torch.empty((n,), dtype=torch.int32, device="cuda"); stt = torch.empty((n,), dtype=torch.int32, device="cuda")
+    rc = lib.b200icp_run_static(vp(pool_t), vp(counts_t), int(pool_t.shape[0]), int(pool_t.shape[1]), dim, vp(pairs_t), vp(init_t),
+                                vp(eps_t), vp(nz), n, 2000, 1e-4, vp(T), vp(er), vp(it), vp(stt), None, None)
+    assert rc == 0, rc
 torch.cuda.synchronize()
 print("sanitize cases done")

@@ -67,7 +67,7 @@ def _slack(d_hi, a_bound):
     u = np.float32(2.0 ** -24)
     s = np.sqrt(np.float32(d_hi))
     a_s = np.float32(a_bound) + s
-    return np.float32(8) * u * a_s * s + np.float32(8) * u * np.float32(d_hi) + np.float32(8) * u * u * a_s * a_s
+    return np.float32(8) * u * a_s * s + np.float32(8) * u * np.float32(d_hi) + np.float32(8) * u * u * a_s * a_s + np.float32(1.1754944e-38)
 
 
 @pytest.mark.parametrize("dim,scale", [(2, 5.0), (2, 30.0), (3, 1.0), (3, 1000.0), (2, 1e-3)])
