@@ -467,17 +467,28 @@ def run_b200_arm(args):
     if world > 1:
         d2h_bytes += host_out.numel() * 8
 
+    # At N > 1 the wait for step k's rows is issued after the launch of step k + 1 (PeerGather.DEPTH = 4 row
+    # slots make that safe): a rank whose batch has the shorter queue tail starts its next step instead of
+    # idling until the slowest rank of THIS step has raised its flag.  flush_exchange() waits for the last step.
+    pending = {"dev": None, "e2e": None}
+
+    def flush_exchange(which):
+        tok, pending[which] = pending[which], None
+        return pg.wait(tok) if (pg is not None and tok is not None) else None
+
     def step_device(k):
         """config 2 with the point pool resident in HBM; at N > 1 all poses end up on every rank"""
         pl = pools[k % N_POOLS]
         kw = {}
         if pg is not None:
-            ptrs, flag, parity = pg.begin()
+            ptrs, flag, token = pg.begin()
             kw = dict(peer_pose_ptrs=ptrs, peer_row0=rank * B, peer_flag=flag)
         res = engine.run_icp_batch(pl["scans"], pl["counts"], pl["pairs"], pl["init"], epsilon=EPSILON,
                                    max_iters=MAX_ITERS, stopping_thresh=STOP, planar_fallback=False, **kw)
         if pg is not None:
-            return res, pg.wait(parity)
+            prev = flush_exchange("dev")          # rows of step k - 1
+            pending["dev"] = token
+            return res, prev
         if world > 1:
             dist.all_gather_into_tensor(gathered, engine.pack_poses(res.T, res.error))
             return res, gathered
@@ -488,15 +499,17 @@ def run_b200_arm(args):
         hp = host[k % N_POOLS]
         kw = {}
         if pg is not None:
-            ptrs, flag, parity = pg.begin()
+            ptrs, flag, token = pg.begin()
             kw = dict(peer_pose_ptrs=ptrs, peer_row0=rank * B, peer_flag=flag)
         res, _ = hostapi.run_icp_ranges_host(hp["ranges"], hp["pairs"], hp["init"], epsilon=EPSILON, max_iters=MAX_ITERS,
                                              stopping_thresh=STOP, range_min=RANGE_MIN, range_max=RANGE_MAX, out=host_ws,
                                              tables=tables, **kw)
         if pg is not None:
-            rows = pg.wait(parity)
-            host_out.copy_(rows, non_blocking=True)
-            torch.cuda.synchronize()
+            rows = flush_exchange("e2e")          # every rank's rows of the PREVIOUS step, to the host
+            pending["e2e"] = token
+            if rows is not None:
+                host_out.copy_(rows, non_blocking=True)
+                torch.cuda.synchronize()
         elif world > 1:
             local_rows = torch.from_numpy(np.concatenate([res.T[:, 0, 3:4], res.T[:, 1, 3:4],
                                                           np.arctan2(res.T[:, 1, 0:1], res.T[:, 0, 0:1]),
@@ -527,6 +540,8 @@ def run_b200_arm(args):
     for k in range(n_warm):
         results[k % N_POOLS], rows_seen = step_device(k)
         tiles[k % N_POOLS] = engine.swept_tiles()      # (32 x 32)-candidate tiles the kernel really swept
+    if pg is not None:
+        rows_seen = flush_exchange("dev")              # the rows of the last warm-up step
     barrier()
     last_k = (n_warm - 1) % N_POOLS
     last = results[last_k]
@@ -592,6 +607,7 @@ def run_b200_arm(args):
     ev0.record()
     for k in range(args.steps):
         step_device(k)
+    flush_exchange("dev")                              # the last step's rows have arrived inside the timed region
     ev1.record()
     barrier()
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
@@ -656,12 +672,17 @@ def run_b200_arm(args):
     e2e_res = None
     for k in range(3):
         e2e_res = step_e2e(k)
+    flush_exchange("e2e")
     if not np.array_equal(e2e_res.T, results[2 % N_POOLS].T.cpu().numpy()):
         raise RuntimeError("b200icp_run_host_ranges disagrees with the device entry on the bench batch")
     barrier()
     ev0.record()
     for k in range(args.steps):
         step_e2e(k)
+    last_rows = flush_exchange("e2e")
+    if last_rows is not None:
+        host_out.copy_(last_rows, non_blocking=True)
+        torch.cuda.synchronize()
     ev1.record()
     barrier()
     ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
@@ -745,7 +766,8 @@ def run_b200_arm(args):
                          f"(> 126 MB L2 together)",
                    "exchange": ("none (1 GPU)" if world == 1 else
                                 "fused: peer stores of [B,4] f64 rows + one arrival flag per rank from the ICP kernel's epilogue into "
-                                "every rank's symmetric-memory buffer over NVLink, a stream-ordered flag wait, no host-side barrier"
+                                "every rank's symmetric-memory buffer over NVLink (4 row slots used in turn), a stream-ordered flag wait issued "
+                                "after the NEXT step's launch (the last step's wait is inside the timed region), no host-side barrier"
                                 if pg is not None else "pack_poses + one NCCL all_gather_into_tensor of [B,4] f64 per step"),
                    "exchange_check": exchange_check, "all_pairs_converged": ok, "parity_sample_ok": parity2,
                    "parity_sample": "16 pairs of the bench batch vs oracle/icp_oracle.py (passes equal, |dT| < 1e-9)"},

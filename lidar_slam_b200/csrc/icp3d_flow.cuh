@@ -474,100 +474,44 @@ __device__ __forceinline__ double warp_min_f64(double v) { return -warp_max_f64(
 #define FLOW_CNT(i) do { } while (0)
 #endif
 
-// Pop one work item from the global ring (one lane).  kRingEmpty: every pair is finished (or the launch
-// was aborted) -- nothing will ever be queued again.
-__device__ __forceinline__ unsigned flow_pop_global(unsigned* ctl, unsigned* ring, const FlowLayout& L) {
-  unsigned item = kRingEmpty;
-  const unsigned ticket = atomicAdd(&ctl[kCtlHead], 1u);
-  unsigned* slot = ring + (ticket & (unsigned)(L.ring_cap - 1));
-  unsigned long long t0 = 0;
-  for (unsigned spins = 0;; ++spins) {
-    const unsigned v = ld_volatile_u32(slot);
-    if (v != kRingEmpty && atomicCAS(slot, v, kRingEmpty) == v) { item = v; break; }
-    if (ld_volatile_u32(&ctl[kCtlPairsDone]) >= (unsigned)L.n_pairs || ld_volatile_u32(&ctl[kCtlAbort]) != 0u) break;
-    if (spins > 16u) {
-      __nanosleep(200);
-      if (t0 == 0) t0 = global_timer_ns();
-      else if (global_timer_ns() - t0 > kFlowSpinLimitNs) { atomicExch(&ctl[kCtlAbort], 1u); break; }
-    }
-  }
-  __threadfence();      // acquire: the state the producer published before the item
-  return item;
-}
-
-// The warps of a CTA are decoupled (round 2b; the CTA-wide barriers around every item were 57 % of the
-// stall samples, profiles/r2_icp3d_flow_*): a CTA-local ticket gives a warp (item number, row of the
-// item); the warp that first needs an item that is not there yet pops it from the global ring and
-// publishes it in one of kFlowDepth shared slots; every row writes its partial sums into the slot, and
-// the warp that delivers the LAST row of an item adds the rows in row order (the same order as before:
-// results unchanged bit for bit), hands the chunk over and, when it retires the last chunk of a pass,
-// solves and queues the next pass -- while the other warps are already on the next items.
-constexpr int kFlowDepth = 4;
-static_assert(kFlowWarps == 8, "tickets encode the row of an item in 3 bits");
-
 template <bool PRUNE>
 __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const RunParams p, const FlowLayout L, char* ws) {
-  __shared__ unsigned s_items[kFlowDepth];          // item published in the slot
-  __shared__ unsigned s_arrive[kFlowDepth];         // rows of the slot's item delivered so far
-  __shared__ unsigned s_gen[kFlowDepth];            // CTA-local number of the item that may use the slot
-  __shared__ unsigned s_ready;                      // items published so far (numbers 0 .. s_ready - 1)
-  __shared__ unsigned s_stop;                       // the global ring has run dry for good
-  __shared__ unsigned s_ticket;                     // next (item number, row)
-  __shared__ unsigned s_lock;                       // one popper at a time
-  __shared__ double s_part[kFlowDepth][kFlowWarps][kRed3d];
+  __shared__ unsigned s_item;
+  __shared__ double s_part[kFlowWarps][kRed3d];
   unsigned* ctl = reinterpret_cast<unsigned*>(ws);
   FlowPair* ps = reinterpret_cast<FlowPair*>(ws + L.off_pairs);
   unsigned* ring = reinterpret_cast<unsigned*>(ws + L.off_ring);
   double* part = reinterpret_cast<double*>(ws + L.off_part);
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned full = 0xffffffffu;
   const float kInfF = __int_as_float(0x7f800000);
   const double kInf = __longlong_as_double(0x7ff0000000000000LL);
   unsigned tiles = 0;
-  if (tid < kFlowDepth) { s_items[tid] = kRingEmpty; s_arrive[tid] = 0u; s_gen[tid] = (unsigned)tid; }
-  if (tid == 0) { s_ready = 0u; s_stop = 0u; s_ticket = 0u; s_lock = 0u; }
-  __syncthreads();
-  volatile unsigned* v_ready = &s_ready;
-  volatile unsigned* v_stop = &s_stop;
-  volatile unsigned* v_gen = s_gen;
-  volatile unsigned* v_items = s_items;
 
   for (;;) {
-    // ---- ticket: (item number of this CTA, row of the item) ------------------------------------
-    unsigned item = kRingEmpty, tk = 0;
-    if (lane == 0) {
-      tk = atomicAdd(&s_ticket, 1u);
-      const unsigned idx = tk >> 3;
-      for (;;) {
-        if (*v_ready > idx) { __threadfence_block(); item = v_items[idx & (kFlowDepth - 1)]; break; }
-        if (*v_stop != 0u) break;
-        if (atomicCAS(&s_lock, 0u, 1u) == 0u) {
-          // popper: publish the NEXT unpublished item (its number may be below this warp's own)
-          const unsigned n = *v_ready;
-          if (n <= idx && *v_stop == 0u) {
-            const unsigned ns_ = n & (kFlowDepth - 1);
-            while (v_gen[ns_] != n) __nanosleep(40);      // hand-off of item n - kFlowDepth has read the slot
-            const unsigned got = flow_pop_global(ctl, ring, L);
-            if (got == kRingEmpty) {
-              *v_stop = 1u;
-            } else {
-              v_items[ns_] = got;
-              __threadfence_block();
-              *v_ready = n + 1u;
-            }
-          }
-          __threadfence_block();
-          atomicExch(&s_lock, 0u);
-        } else {
-          __nanosleep(40);
+    // ---- pop a work item ----------------------------------------------------------------------
+    FLOW_DBG(1);
+    if (tid == 0) {
+      unsigned item = kRingEmpty;
+      const unsigned ticket = atomicAdd(&ctl[kCtlHead], 1u);
+      unsigned* slot = ring + (ticket & (unsigned)(L.ring_cap - 1));
+      unsigned long long t0 = 0;
+      for (unsigned spins = 0;; ++spins) {
+        const unsigned v = ld_volatile_u32(slot);
+        if (v != kRingEmpty && atomicCAS(slot, v, kRingEmpty) == v) { item = v; break; }
+        if (ld_volatile_u32(&ctl[kCtlPairsDone]) >= (unsigned)L.n_pairs || ld_volatile_u32(&ctl[kCtlAbort]) != 0u) break;
+        if (spins > 16u) {
+          __nanosleep(200);
+          if (t0 == 0) t0 = global_timer_ns();
+          else if (global_timer_ns() - t0 > kFlowSpinLimitNs) { atomicExch(&ctl[kCtlAbort], 1u); break; }
         }
       }
+      __threadfence();      // acquire: the state the producer published before the item
+      s_item = item;
     }
-    item = __shfl_sync(full, item, 0);
-    tk = __shfl_sync(full, tk, 0);
+    __syncthreads();
+    const unsigned item = s_item;
     if (item == kRingEmpty) break;
-    const unsigned islot = (tk >> 3) & (kFlowDepth - 1);
-    const int irow = (int)(tk & 7u);
     FLOW_DBG(2); FLOW_CNT(0);
     const int pair = (int)(item >> 21), chunk = (int)(item & 0x1fffffu);
     FlowPair* P = ps + pair;
@@ -593,7 +537,7 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
 #pragma unroll
     for (int k = 0; k < 3; ++k) { acc[kSums3d + 2 * k] = kInf; acc[kSums3d + 2 * k + 1] = -kInf; }
 
-    const int row = chunk * kFlowWarps + irow;
+    const int row = chunk * kFlowWarps + warp;
     if (row * kFlowRowQ < ns) {
       // ---- this warp's row: two queries per lane -------------------------------------------
       const int j0 = row * kFlowRowQ + lane;
@@ -790,42 +734,24 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
     }
     if (lane == 0) {
 #pragma unroll
-      for (int k = 0; k < kRed3d; ++k) s_part[islot][irow][k] = acc[k];
+      for (int k = 0; k < kRed3d; ++k) s_part[warp][k] = acc[k];
     }
     FLOW_DBG(3);
-    __syncwarp();
-    unsigned arrived = 0;
-    if (lane == 0) {
-      __threadfence_block();
-      arrived = atomicAdd(&s_arrive[islot], 1u);
-    }
-    arrived = __shfl_sync(full, arrived, 0);
-    if (arrived != (unsigned)(kFlowWarps - 1)) continue;      // not the last row of the item: next ticket
-    __threadfence_block();
+    __syncthreads();
+    if (warp != 0) continue;          // warps 1..7 wait for the next item at the barrier above
     FLOW_DBG_W0(4);
 
-    // ---- the warp that delivered the last row: this chunk's partial sums (rows in row order) to
-    //      global memory; the slot is free again as soon as they are read; retire the chunk ----------
+    // ---- warp 0: this chunk's partial sums to global memory; retire the chunk -------------------
     const bool is_min = lane >= kSums3d && ((lane - kSums3d) & 1) == 0;
     const bool is_max = lane >= kSums3d && ((lane - kSums3d) & 1) == 1;
-    {
-      double v = 0.0;
-      if (lane < kRed3d) {
-        const volatile double* sp = &s_part[islot][0][0];
-        v = sp[lane];
+    if (lane < kRed3d) {
+      double v = s_part[0][lane];
 #pragma unroll
-        for (int w = 1; w < kFlowWarps; ++w) {
-          const double o = sp[w * kRed3d + lane];
-          v = is_min ? fmin(v, o) : (is_max ? fmax(v, o) : v + o);
-        }
-        __stcg(part + ((size_t)pair * L.max_chunks + chunk) * kRed3d + lane, v);
+      for (int w = 1; w < kFlowWarps; ++w) {
+        const double o = s_part[w][lane];
+        v = is_min ? fmin(v, o) : (is_max ? fmax(v, o) : v + o);
       }
-      __syncwarp();
-      if (lane == 0) {
-        s_arrive[islot] = 0u;
-        __threadfence_block();
-        v_gen[islot] = (tk >> 3) + (unsigned)kFlowDepth;
-      }
+      __stcg(part + ((size_t)pair * L.max_chunks + chunk) * kRed3d + lane, v);
     }
     __threadfence();
     __syncwarp();

@@ -398,21 +398,26 @@ def shard_range(n_items: int, rank: int, world: int):
 
 
 _PEER_BUFFERS = {}
-_FLAG_WORDS = 16          # one uint32 arrival flag per rank (<= 16 ranks), per parity
+_FLAG_WORDS = 16          # one uint32 arrival flag per rank (<= 16 ranks), per row slot
 
 
 class PeerGather:
     """Symmetric-memory gather buffer of the fused pose exchange, shared by all ranks of a group:
-    two row buffers [rows, 4] float64 used alternately (step parity) and one uint32 arrival flag per
-    rank and parity.  Every rank maps every other rank's copy, so a kernel stores rows -- and, when
-    its last pair retires, its flag -- straight into all of them over NVLink.  Protocol of step s
-    (parity p = s & 1, value s + 1), with NO host-side cross-rank barrier:
-      * the ICP launch stores this rank's rows into buffer p of every rank, then flag[p][rank] = s + 1;
-      * `wait()` (a stream-ordered kernel) returns once flag[p][r] >= s + 1 for every rank r: all rows
-        of step s are in this rank's buffer p;
-      * buffer p is written again in step s + 2, which a rank can only start after its wait of step
-        s + 1, i.e. after every rank has launched step s + 1, which in stream order comes after that
-        rank's consumers of step s: double buffering is what makes the pre-launch barrier unnecessary."""
+    DEPTH row buffers [rows, 4] float64 used in turn (step s uses slot s % DEPTH) and one uint32 arrival
+    flag per (slot, source rank).  Every rank maps every other rank's copy, so a kernel stores rows --
+    and, when its last pair retires, its flag -- straight into all of them over NVLink.  Protocol of
+    step s (value s + 1), with NO host-side cross-rank barrier:
+      * the ICP launch stores this rank's rows into slot s % DEPTH of every rank, then flag[slot][rank] = s + 1;
+      * `wait(token)` (a stream-ordered kernel) returns once flag[slot][r] >= s + 1 for every rank r: all
+        rows of step s are in this rank's slot;
+      * the slot is written again in step s + DEPTH.  A caller that waits right after each launch
+        (run_icp_sharded: L(s) W(s) C(s) L(s+1) ...) needs DEPTH >= 2: a peer launches step s + 2 after its
+        wait of step s + 1, i.e. after this rank's kernel s + 1 finished, which in stream order follows
+        this rank's consumers C(s).  A caller that defers the wait by one step to hide the slowest rank
+        (bench.py: L(s+1) W(s) C(s) L(s+2) ...) needs DEPTH >= 4: a peer launches step s + 4 after its wait
+        of step s + 2, i.e. after this rank's kernel s + 2, which is enqueued behind C(s)."""
+
+    DEPTH = 4
 
     def __init__(self, rows: int, dev, group):
         import torch.distributed as dist
@@ -420,7 +425,7 @@ class PeerGather:
         self.rows, self.dev = rows, dev
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
-        n_f64 = 2 * rows * 4 + 2 * _FLAG_WORDS // 2          # rows of both parities + 2 x 16 uint32 flags
+        n_f64 = self.DEPTH * rows * 4 + self.DEPTH * _FLAG_WORDS // 2      # row slots + DEPTH x 16 uint32 flags
         self.buf = symm_mem.empty((n_f64,), dtype=torch.float64, device=dev)
         self.buf.zero_()
         self.hdl = symm_mem.rendezvous(self.buf, group=group if group is not None else dist.group.WORLD)
@@ -431,28 +436,32 @@ class PeerGather:
         self.base_ptrs = [int(q) for q in self.hdl.buffer_ptrs]
 
     def begin(self):
-        """(peer pointers of this step's row buffer, peer_flag triple, parity)"""
-        p = self.step & 1
-        ptrs = [b + p * self.rows * 32 for b in self.base_ptrs]
-        flag_off = (2 - p) * self.rows * 32 + p * 4 * _FLAG_WORDS
-        return ptrs, (flag_off, self.rank, self.step + 1), p
-
-    def rows_view(self, parity, rank=None):
-        """[rows, 4] view of this rank's (or a peer's) row buffer of the given parity."""
-        if rank is None or rank == self.rank:
-            return self.buf[parity * self.rows * 4:(parity + 1) * self.rows * 4].view(self.rows, 4)
-        whole = self.hdl.get_buffer(rank, (self.buf.numel(),), torch.float64)
-        return whole[parity * self.rows * 4:(parity + 1) * self.rows * 4].view(self.rows, 4)
-
-    def wait(self, parity):
-        """Stream-ordered: every rank's rows of the current step have landed in this rank's buffer."""
-        lib = _lib.load()
-        flags_ptr = self.buf.data_ptr() + 2 * self.rows * 32 + parity * 4 * _FLAG_WORDS
-        with torch.cuda.device(self.dev):
-            _lib.check(lib.b200icp_exchange_wait(ctypes.c_void_p(flags_ptr), self.world, self.step + 1, 20000,
-                                                 _ptr(self.timed_out), _stream_ptr()), "b200icp_exchange_wait")
+        """(peer pointers of this step's row slot, peer_flag triple, token for wait / rows_view)"""
+        s = self.step
         self.step += 1
-        return self.rows_view(parity)
+        slot = s % self.DEPTH
+        ptrs = [b + slot * self.rows * 32 for b in self.base_ptrs]
+        # flag offset is relative to the row pointer the kernel gets (the slot's base)
+        flag_off = (self.DEPTH - slot) * self.rows * 32 + slot * 4 * _FLAG_WORDS
+        return ptrs, (flag_off, self.rank, s + 1), (slot, s)
+
+    def rows_view(self, token, rank=None):
+        """[rows, 4] view of this rank's (or a peer's) row slot of the step `token` names."""
+        slot = token[0] if isinstance(token, tuple) else int(token)
+        if rank is None or rank == self.rank:
+            return self.buf[slot * self.rows * 4:(slot + 1) * self.rows * 4].view(self.rows, 4)
+        whole = self.hdl.get_buffer(rank, (self.buf.numel(),), torch.float64)
+        return whole[slot * self.rows * 4:(slot + 1) * self.rows * 4].view(self.rows, 4)
+
+    def wait(self, token):
+        """Stream-ordered: every rank's rows of the step `token` names have landed in this rank's slot."""
+        slot, s = token
+        lib = _lib.load()
+        flags_ptr = self.buf.data_ptr() + self.DEPTH * self.rows * 32 + slot * 4 * _FLAG_WORDS
+        with torch.cuda.device(self.dev):
+            _lib.check(lib.b200icp_exchange_wait(ctypes.c_void_p(flags_ptr), self.world, s + 1, 20000,
+                                                 _ptr(self.timed_out), _stream_ptr()), "b200icp_exchange_wait")
+        return self.rows_view(slot)
 
     def check(self):
         if int(self.timed_out.item()) != 0:
@@ -480,7 +489,7 @@ def run_icp_sharded(scans, counts, pairs, init_transforms=None, group=None, exch
     exchange="nccl": pack_poses + ONE all_gather_into_tensor (NCCL on GPUs, gloo in the CPU tests of
     the host logic).  "auto" = "peer" on CUDA with NCCL when symmetric memory is available, else "nccl".
     Returns (rows [B,4], local IcpBatchResult); with "peer" the rows alias the cached buffer and
-    are valid until the sharded call after the next one of the same shape (two buffers alternate).
+    are valid until PeerGather.DEPTH - 1 further sharded calls of the same shape (the row slots are used in turn).
     """
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_initialized() else 1
