@@ -503,7 +503,7 @@ def run_b200_arm(args):
             kw = dict(peer_pose_ptrs=ptrs, peer_row0=rank * B, peer_flag=flag)
         res, _ = hostapi.run_icp_ranges_host(hp["ranges"], hp["pairs"], hp["init"], epsilon=EPSILON, max_iters=MAX_ITERS,
                                              stopping_thresh=STOP, range_min=RANGE_MIN, range_max=RANGE_MAX, out=host_ws,
-                                             tables=tables, **kw)
+                                             **kw)
         if pg is not None:
             rows = flush_exchange("e2e")          # every rank's rows of the PREVIOUS step, to the host
             pending["e2e"] = token

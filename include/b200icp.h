@@ -277,6 +277,14 @@ int b200icp_run_pair_host(const double* src, int n_src, const double* tgt, int n
                           int32_t* status_out, int32_t* corr_out);
 int b200icp_host_release(void);
 
+/* Page-locked host memory for the arrays handed to the host entries (cudaHostAlloc / cudaFreeHost).
+ * Optional: the host entries accept any host pointer, but copies from and to pageable memory are
+ * staged by the driver and block the calling thread, which costs the overlap the entries are built
+ * for.  lidar_slam_b200.hostapi keeps its reusable result buffers in memory from here.  No counterpart
+ * in the reference (numpy arrays are pageable).  b200icp_host_alloc returns NULL on failure. */
+void* b200icp_host_alloc(size_t bytes);
+int b200icp_host_free(void* p);
+
 /* b200icp_run without a workspace argument, for callers that cannot allocate device memory at all
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  * NO COUNTERPART IN THE REFERENCE: this entry was added.

@@ -21,6 +21,8 @@ SIGNATURES = {
     "b200icp_run": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200icp_host_alloc": (c_void_p, [c_size_t]),
+    "b200icp_host_free": (c_int, [c_void_p]),
     "b200icp_run_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),

@@ -67,11 +67,22 @@ template <int W, int R, int MINB, bool PRUNE, bool RANGES>
 int launch_rows_variant(const RunParams& p, cudaStream_t stream, int sms) {
   auto kern = icp2d_rows_kernel<W, R, MINB, PRUNE, RANGES>;
   const Rows2dLayout L = rows2d_layout(p.n_max, W, RANGES);
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
-    return B200ICP_ERR_CUDA;
-  int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, L.total) != cudaSuccess || per_sm < 1)
-    return B200ICP_ERR_CUDA;
+  // attribute + occupancy of this instantiation, remembered per device for the last n_max (a caller
+  // that loops over one batch shape pays the two runtime queries once; a racing first call repeats them)
+  struct Cached { int n_max = 0, per_sm = 0; };
+  static Cached cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return B200ICP_ERR_NO_DEVICE;
+  int per_sm = cached[dev].n_max == p.n_max ? cached[dev].per_sm : 0;
+  if (per_sm < 1) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
+      return B200ICP_ERR_CUDA;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W * 32, L.total) != cudaSuccess || per_sm < 1)
+      return B200ICP_ERR_CUDA;
+    cached[dev].per_sm = 0;
+    cached[dev].n_max = p.n_max;
+    cached[dev].per_sm = per_sm;
+  }
   const long long resident = (long long)per_sm * sms;
   const int grid = (int)(p.n_pairs < resident ? p.n_pairs : resident);
   kern<<<grid, W * 32, L.total, stream>>>(p);

@@ -179,7 +179,11 @@ int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
   // The slices are ENQUEUED before the launch: if something serialises launches (a profiler,
   // CUDA_LAUNCH_BLOCKING) the kernel must never wait for a copy the host has not issued yet.
   int n_slices = (int)((io.flags >> 8) & 0xffu);
-  if (n_slices == 0) n_slices = 24;
+  // Default: 16 equal slices for range rows, 24 for points.  Measured (profiles/r2_host_entry_slices.txt):
+  // 8..32 equal slices are within 1.5 % of each other; 12 slices growing by 1.45x (small first slice, fewer
+  // enqueue calls ahead of the launch) were 3 % SLOWER than 16 equal ones although the upload alone runs at
+  // 55 GB/s, twice the rate at which the kernel consumes it -- kept equal.
+  if (n_slices == 0) n_slices = pool.kind != 0 ? 16 : 24;
   if (n_slices > kMaxSlices - 1) n_slices = kMaxSlices - 1;   // the last pinned word receives the gave-up flag
   if (n_slices > pool.n_scans) n_slices = pool.n_scans;
   int copied = 0;
@@ -479,6 +483,19 @@ int b200icp_run_pair_host(const double* src, int n_src, const double* tgt, int n
   if (iters_out) memcpy(iters_out, ho + 136, 4);
   if (status_out) memcpy(status_out, ho + 140, 4);
   if (corr_out) memcpy(corr_out, ho + 144, (size_t)n_src * 4);
+  return B200ICP_OK;
+}
+
+void* b200icp_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (bytes == 0) bytes = 1;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+
+int b200icp_host_free(void* p) {
+  if (!p) return B200ICP_OK;
+  if (cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
   return B200ICP_OK;
 }
 

@@ -9,6 +9,7 @@ the device memory, the host<->device copies and their overlap with the kernels.
 from __future__ import annotations
 
 import ctypes
+import weakref
 from typing import NamedTuple, Optional, Sequence
 
 import numpy as np
@@ -50,6 +51,23 @@ def _per_pair(value, n, dtype):
     if a.shape != (n,):
         raise ValueError("per-pair arguments must be scalars or have one entry per pair")
     return np.ascontiguousarray(a)
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """np.empty in page-locked memory (b200icp_host_alloc): the library's copies from and to it are real
+    asynchronous DMA instead of driver-staged, blocking copies.  Freed when the array is collected.
+    Falls back to pageable memory when the allocation fails (the calls still work, only slower)."""
+    shape = tuple(int(x) for x in (shape if isinstance(shape, (tuple, list)) else (shape,)))
+    dt = np.dtype(dtype)
+    nbytes = max(int(np.prod(shape)) * dt.itemsize, 1)
+    lib = _lib.load()
+    ptr = lib.b200icp_host_alloc(nbytes)
+    if not ptr:
+        return np.empty(shape, dtype=dt)
+    raw = (ctypes.c_char * nbytes).from_address(ptr)
+    arr = np.frombuffer(raw, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+    weakref.finalize(raw, lib.b200icp_host_free, ctypes.c_void_p(ptr))
+    return arr
 
 
 def _p(a: Optional[np.ndarray]):
@@ -122,16 +140,40 @@ def beam_tables(n_beams: int):
 
 
 class HostRangesWorkspace:
-    """Reusable host-side buffers for run_icp_ranges_host (results land in the same arrays on every
-    call, so that a caller who loops pays no allocation; pass `out=` to reuse)."""
+    """Reusable, page-locked host-side buffers for run_icp_ranges_host: results land in the same arrays on
+    every call, so that a caller who loops pays no allocation and the copies back are asynchronous DMA;
+    scalar epsilon / normalize_error are expanded into pinned per-pair arrays kept here.  Pass `out=`."""
 
     def __init__(self, n_pairs: int, n_scans: int, n_max: int, correspondences: bool = False):
-        self.T = np.empty((n_pairs, 4, 4), dtype=np.float64)
-        self.err = np.empty((n_pairs,), dtype=np.float64)
-        self.iters = np.empty((n_pairs,), dtype=np.int32)
-        self.status = np.empty((n_pairs,), dtype=np.int32)
-        self.corr = np.empty((n_pairs, n_max), dtype=np.int32) if correspondences else None
-        self.counts = np.empty((n_scans,), dtype=np.int32)
+        self.T = pinned_empty((n_pairs, 4, 4), np.float64)
+        self.err = pinned_empty((n_pairs,), np.float64)
+        self.iters = pinned_empty((n_pairs,), np.int32)
+        self.status = pinned_empty((n_pairs,), np.int32)
+        self.corr = pinned_empty((n_pairs, n_max), np.int32) if correspondences else None
+        self.counts = pinned_empty((n_scans,), np.int32)
+        self.eps = pinned_empty((n_pairs,), np.float64)
+        self.norm = pinned_empty((n_pairs,), np.uint8)
+        self._tables = {}
+
+    def beam_tables(self, n_beams: int):
+        """beam_tables(n_beams) in pinned memory, computed once."""
+        if n_beams not in self._tables:
+            c, s_ = beam_tables(n_beams)
+            pc, ps = pinned_empty((n_beams,), np.float64), pinned_empty((n_beams,), np.float64)
+            pc[:], ps[:] = c, s_
+            self._tables[n_beams] = (pc, ps)
+        return self._tables[n_beams]
+
+    def per_pair(self, epsilon, normalize_error):
+        """(eps, norm) per-pair arrays: the pinned ones filled with a scalar, or the caller's arrays."""
+        n = self.eps.shape[0]
+        eps = np.asarray(epsilon, dtype=np.float64)
+        if eps.ndim == 0:
+            self.eps.fill(float(eps)); eps = self.eps
+        norm = np.asarray(normalize_error, dtype=np.uint8)
+        if norm.ndim == 0:
+            self.norm.fill(int(norm)); norm = self.norm
+        return _per_pair(eps, n, np.float64), _per_pair(norm, n, np.uint8)
 
 
 def run_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms=None, epsilon=0.01,
@@ -151,19 +193,20 @@ def run_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms=N
         raise ValueError("ranges must be [S, n_beams] with n_beams <= 2048")
     n_scans, n_beams = ranges.shape
     n_max = n_beams + (n_beams & 1)
-    cos_t, sin_t = tables if tables is not None else beam_tables(n_beams)
-    cos_t, sin_t = np.ascontiguousarray(cos_t, dtype=np.float64), np.ascontiguousarray(sin_t, dtype=np.float64)
     pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
     n_pairs = pairs.shape[0]
+    o = out if out is not None else HostRangesWorkspace(n_pairs, n_scans, n_max, return_correspondences)
+    cos_t, sin_t = tables if tables is not None else o.beam_tables(n_beams)
+    cos_t, sin_t = np.ascontiguousarray(cos_t, dtype=np.float64), np.ascontiguousarray(sin_t, dtype=np.float64)
     if init_transforms is None:
         init = np.broadcast_to(np.eye(4), (n_pairs, 4, 4)).copy()
     else:
         init = np.ascontiguousarray(init_transforms, dtype=np.float64).reshape(-1, 4, 4)
         if init.shape[0] != n_pairs:
             raise ValueError("init_transforms must have one 4x4 per pair")
-    eps = _per_pair(epsilon, n_pairs, np.float64)
-    norm = _per_pair(normalize_error, n_pairs, np.uint8)
-    o = out if out is not None else HostRangesWorkspace(n_pairs, n_scans, n_max, return_correspondences)
+    if o.T.shape[0] != n_pairs or o.counts.shape[0] != n_scans or (return_correspondences and o.corr is None):
+        raise ValueError("`out` was built for another batch shape")
+    eps, norm = o.per_pair(epsilon, normalize_error)
     ex, keep = _lib.make_exchange(peer_pose_ptrs, peer_row0, *(peer_flag or (0, 0, 0)))
     _lib.check(lib.b200icp_run_host_ranges(
         _p(ranges), 1 if ranges.dtype == np.float32 else 0, n_scans, n_beams, _p(cos_t), _p(sin_t), float(range_min),

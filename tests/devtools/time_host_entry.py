@@ -22,7 +22,18 @@ for _ in range(10):
     engine.run_icp_ranges_batch(dev_r, torch.as_tensor(pairs).cuda(), torch.as_tensor(init).cuda(), epsilon=1e-3)
 ev[1].record(); torch.cuda.synchronize()
 print(f"resident ranges kernel (+ small uploads): {ev[0].elapsed_time(ev[1]) / 10:.3f} ms")
-for slices in (0, 2, 4, 6, 8, 12, 16, 24, 32, 48):
+# the upload alone: one pinned -> device copy of the range rows
+src_t, dst_t = torch.as_tensor(ranges), torch.empty_like(dev_r)
+for _ in range(3):
+    dst_t.copy_(src_t, non_blocking=True)
+torch.cuda.synchronize()
+ev[0].record()
+for _ in range(10):
+    dst_t.copy_(src_t, non_blocking=True)
+ev[1].record(); torch.cuda.synchronize()
+ms_copy = ev[0].elapsed_time(ev[1]) / 10
+print(f"upload alone: {ranges.nbytes / 1e6:.1f} MB in {ms_copy:.3f} ms = {ranges.nbytes / ms_copy / 1e6:.1f} GB/s")
+for slices in (0, 4, 8, 12, 16, 24, 32):
     fl = _lib.flag_slices(slices) if slices else 0
     best, tot = 1e9, 0.0
     for rep in range(14):
