@@ -524,10 +524,16 @@ def run_b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(ms):
+    by_rank = {}
+
+    def max_over_ranks(ms, tag=None):
         if world == 1:
             return ms
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if tag is not None:          # every rank's own device time, for the JSON line (ranks hold different data)
+            every = torch.empty((world,), dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(every, t)
+            by_rank[tag] = [round(float(x), 3) for x in every.tolist()]
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
@@ -610,7 +616,7 @@ def run_b200_arm(args):
     flush_exchange("dev")                              # the last step's rows have arrived inside the timed region
     ev1.record()
     barrier()
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1), "resident")
 
     # ---- the dominant kernel alone (CUDA events on the launching stream) ----
     barrier()
@@ -685,7 +691,7 @@ def run_b200_arm(args):
         torch.cuda.synchronize()
     ev1.record()
     barrier()
-    ms_e2e = max_over_ranks(ev0.elapsed_time(ev1))
+    ms_e2e = max_over_ranks(ev0.elapsed_time(ev1), "e2e")
     if pg is not None:
         pg.check()
 
@@ -779,6 +785,9 @@ def run_b200_arm(args):
         "dropin_ms_per_call": dropin_ms,
         "clocks": clocks,
     }
+    if by_rank:
+        line["ms_total_by_rank"] = dict(by_rank, note="each rank's own device time for the timed steps (value uses the max): the ranks "
+                                                      "align different synthetic trajectories (seed + 1000 rank), so their queue tails differ")
     if two_stream_ms is not None:
         line["two_stream_value"] = {
             "value": B * args.steps / (two_stream_ms * 1e-3), "unit": UNIT, "ms_per_step": two_stream_ms / args.steps,
