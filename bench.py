@@ -632,6 +632,8 @@ def run_b200_arm(args):
         kernel_ms += kev[k][0].elapsed_time(kev[k][1])
         kernel_cand += cand[k % N_POOLS]
         kernel_eval += 1024.0 * tiles[k % N_POOLS]
+    if world > 1:
+        max_over_ranks(kernel_ms, "kernel_alone_no_exchange")     # per-rank: how much the ranks' batches differ
     # the exhaustive register-tiled kernel (every candidate evaluated; the north-star "brute-force
     # argmin" variant): the FP32-issue figure of the sweep itself, timed the same way on a few launches
     exh_steps = min(args.steps, 6)
