@@ -63,10 +63,10 @@ int launch2d_variant(const RunParams& p, cudaStream_t stream, int sms) {
 }
 
 // The shipped planar kernel (icp2d_rows.cuh): W warps per pair, R queries per lane.
-template <int W, int R, int MINB, bool PRUNE, bool RANGES>
+template <int W, int R, int MINB, bool PRUNE, bool RANGES, bool SRCG = false>
 int launch_rows_variant(const RunParams& p, cudaStream_t stream, int sms) {
-  auto kern = icp2d_rows_kernel<W, R, MINB, PRUNE, RANGES>;
-  const Rows2dLayout L = rows2d_layout(p.n_max, W, RANGES);
+  auto kern = icp2d_rows_kernel<W, R, MINB, PRUNE, RANGES, SRCG>;
+  const Rows2dLayout L = rows2d_layout(p.n_max, W, RANGES, SRCG);
   // attribute + occupancy of this instantiation, remembered per device for the last n_max (a caller
   // that loops over one batch shape pays the two runtime queries once; a racing first call repeats them)
   struct Cached { int n_max = 0, per_sm = 0; };
@@ -176,6 +176,9 @@ int dispatch(RunParams& p, int dim, void* workspace, size_t workspace_bytes, cud
           case 6: return launch_rows_variant<3, 1, 5, true, false>(p, stream, d.sms);
           case 7: return launch_rows_variant<4, 3, 4, true, false>(p, stream, d.sms);
           case 8: return launch_rows_variant<2, 1, 8, true, false>(p, stream, d.sms);
+          case 9: return launch_rows_variant<4, 1, 5, true, false, true>(p, stream, d.sms);
+          case 10: return launch_rows_variant<4, 1, 4, true, false, true>(p, stream, d.sms);
+          case 11: return launch_rows_variant<4, 1, 6, true, false, true>(p, stream, d.sms);
           default: break;
         }
 #endif

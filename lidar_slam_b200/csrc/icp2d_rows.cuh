@@ -39,12 +39,12 @@ struct Rows2dLayout {
   int np;   // padded point capacity (multiple of 64)
   size_t off_t64, off_s64, off_t32, off_bb, off_red, off_corr, off_rows, off_ctl, total;
 };
-__host__ __device__ inline Rows2dLayout rows2d_layout(int n_max, int warps, bool ranges) {
+__host__ __device__ inline Rows2dLayout rows2d_layout(int n_max, int warps, bool ranges, bool src_global = false) {
   Rows2dLayout L;
   L.np = ((n_max + 63) / 64) * 64;
   size_t o = 0;
   L.off_t64 = o; o += (size_t)L.np * 16;
-  L.off_s64 = o; o += (size_t)L.np * 16;
+  L.off_s64 = o; o += src_global ? 0 : (size_t)L.np * 16;    // SRCG: the source stays in the pool (L1/L2)
   L.off_t32 = o; o += (size_t)L.np * 8;
   L.off_bb = o; o += (size_t)64 * 16;                        // target-block boxes (xmin, xmax, ymin, ymax)
   L.off_red = o; o += (size_t)2 * warps * kRed2d * 8;        // per-pass exchange, double-buffered
@@ -105,12 +105,17 @@ __device__ __forceinline__ double load_range(const RunParams& p, int scan, int b
 
 // W warps per CTA, R queries per lane; PRUNE = false sweeps every block (same bits; A/B and tests);
 // RANGES: the pool is [n_scans, n_beams] ranges, the scans are built here.
-template <int W, int R, int MINB, bool PRUNE, bool RANGES>
+// SRCG (points in only): the float64 source is read from the pool in global memory (each pass reads
+// every source point once, coalesced, L1-resident after the first pass) instead of a shared copy:
+// 30 KB instead of 47 KB per CTA at 1081 points, so that a fifth CTA fits per SM.
+template <int W, int R, int MINB, bool PRUNE, bool RANGES, bool SRCG = false>
 __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParams p) {
+  static_assert(!(RANGES && SRCG), "ranges-in builds the source in shared memory");
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const Rows2dLayout L = rows2d_layout(p.n_max, W, RANGES);
+  const Rows2dLayout L = rows2d_layout(p.n_max, W, RANGES, SRCG);
   double2* t64 = reinterpret_cast<double2*>(smem_raw + L.off_t64);
-  double2* s64 = reinterpret_cast<double2*>(smem_raw + L.off_s64);
+  double2* s64 = reinterpret_cast<double2*>(smem_raw + L.off_s64);       // unused with SRCG
+  const double2* src_pts = s64;
   float* t32 = reinterpret_cast<float*>(smem_raw + L.off_t32);
   float4* bb = reinterpret_cast<float4*>(smem_raw + L.off_bb);
   double* red = reinterpret_cast<double*>(smem_raw + L.off_red);
@@ -281,10 +286,11 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
         __syncthreads();
       } else {
         // ---- stage both scans with TMA bulk copies --------------------------------
+        if constexpr (SRCG) src_pts = reinterpret_cast<const double2*>(p.scans) + (size_t)si * p.n_max;
         if (tid == 0) {
           fence_proxy_async();
-          mbar_expect_tx(mbar, (uint32_t)(ns + nt) * 16u);
-          tma_load_1d(s64, p.scans + (size_t)si * p.n_max * 2, (uint32_t)ns * 16u, mbar);
+          mbar_expect_tx(mbar, (uint32_t)((SRCG ? 0 : ns) + nt) * 16u);
+          if constexpr (!SRCG) tma_load_1d(s64, p.scans + (size_t)si * p.n_max * 2, (uint32_t)ns * 16u, mbar);
           tma_load_1d(t64, p.scans + (size_t)ti * p.n_max * 2, (uint32_t)nt * 16u, mbar);
         }
         mbar_wait(mbar, parity);
@@ -379,7 +385,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
         for (int q = 0; q < R; ++q) {
           // ragged tail: slots past the scan repeat its last point (no predicates below; they are
           // left out of the sums)
-          const double2 s = s64[min(j0 + 32 * q, ns - 1)];
+          const double2 s = src_pts[min(j0 + 32 * q, ns - 1)];
           qdx[q] = fma(r00, s.x, fma(r01, s.y, tx));
           qdy[q] = fma(r10, s.x, fma(r11, s.y, ty));
           fqx[q] = (float)qdx[q]; fqy[q] = (float)qdy[q];
@@ -548,7 +554,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
           for (int q = 0; q < R; ++q) {
             const int j = row * kRowQ + 32 * q + lane;
             if (j < ns) {
-              const double2 s = s64[j];
+              const double2 s = src_pts[j];
               const double x = fma(r00, s.x, fma(r01, s.y, tx)), y = fma(r10, s.x, fma(r11, s.y, ty));
               const double2 t = t64[corr_s[j]];
               mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
