@@ -38,7 +38,15 @@
 namespace b200icp {
 
 constexpr int kFlowWarps = 8;                      // warps per CTA = rows per work item
-constexpr int kFlowRowQ = 64;                      // source points per row (two per lane)
+#ifndef B200ICP_FLOW_Q
+#define B200ICP_FLOW_Q 2
+#endif
+#ifndef B200ICP_FLOW_MINB
+#define B200ICP_FLOW_MINB 2
+#endif
+constexpr int kFlowQ = B200ICP_FLOW_Q;             // source points per lane and row
+constexpr int kFlowMinBlocks = B200ICP_FLOW_MINB;  // resident CTAs per SM the registers are bounded for
+constexpr int kFlowRowQ = 32 * kFlowQ;             // source points per row
 constexpr int kFlowChunkPts = kFlowWarps * kFlowRowQ;
 constexpr int kFlowMaxPairs = 1024;                // pairs per launch; longer lists are cut by the host side
 constexpr int kSums3d = 16;                        // sum u(3) v(3) u v^T(9) sse
@@ -409,16 +417,16 @@ __device__ __forceinline__ float box_lb3(float qlx, float qly, float qlz, float 
 // One 32-target block against the two queries of every lane; targets come from L1/L2 (uniform
 // addresses: every load is a warp-wide broadcast).  Tracks, per query, the best block (value, id,
 // minima of its eight groups of four) and the smallest minimum of any OTHER swept block.
-__device__ __forceinline__ bool flow_sweep_block(const float* t32, int b, const f32x2 (&qxx)[2], const f32x2 (&qyy)[2],
-                                                 const f32x2 (&qzz)[2], float (&bestv)[2], float (&secondv)[2],
-                                                 int (&bestb)[2], float (&gbest)[2][8]) {
+__device__ __forceinline__ bool flow_sweep_block(const float* t32, int b, const f32x2 (&qxx)[kFlowQ], const f32x2 (&qyy)[kFlowQ],
+                                                 const f32x2 (&qzz)[kFlowQ], float (&bestv)[kFlowQ], float (&secondv)[kFlowQ],
+                                                 int (&bestb)[kFlowQ], float (&gbest)[kFlowQ][8]) {
   const ulonglong2* tb = reinterpret_cast<const ulonglong2*>(t32 + (size_t)b * 96);
-  float gm[2][8];
+  float gm[kFlowQ][8];
 #pragma unroll
   for (int g = 0; g < 8; ++g) {
     const ulonglong2 X = __ldg(tb + 3 * g), Y = __ldg(tb + 3 * g + 1), Z = __ldg(tb + 3 * g + 2);
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
+    for (int q = 0; q < kFlowQ; ++q) {
       f32x2 dx = sub2(qxx[q], X.x), dy = sub2(qyy[q], Y.x), dz = sub2(qzz[q], Z.x);
       const f32x2 d01 = fma2(dx, dx, fma2(dy, dy, mul2(dz, dz)));
       dx = sub2(qxx[q], X.y); dy = sub2(qyy[q], Y.y); dz = sub2(qzz[q], Z.y);
@@ -431,7 +439,7 @@ __device__ __forceinline__ bool flow_sweep_block(const float* t32, int b, const 
   }
   bool improved = false;
 #pragma unroll
-  for (int q = 0; q < 2; ++q) {
+  for (int q = 0; q < kFlowQ; ++q) {
     const float bm = fminf(fmin3(fmin3(fmin3(gm[q][0], gm[q][1], gm[q][2]), gm[q][3], gm[q][4]), gm[q][5], gm[q][6]),
                            gm[q][7]);
     if (bm < bestv[q]) {        // strict: on equal minima the earlier (lower) block stays the best one
@@ -475,7 +483,7 @@ __device__ __forceinline__ double warp_min_f64(double v) { return -warp_max_f64(
 #endif
 
 template <bool PRUNE>
-__global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const RunParams p, const FlowLayout L, char* ws) {
+__global__ void __launch_bounds__(kFlowWarps * 32, kFlowMinBlocks) icp3d_flow_kernel(const RunParams p, const FlowLayout L, char* ws) {
   __shared__ unsigned s_item;
   __shared__ double s_part[kFlowWarps][kRed3d];
   unsigned* ctl = reinterpret_cast<unsigned*>(ws);
@@ -541,11 +549,11 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
     if (row * kFlowRowQ < ns) {
       // ---- this warp's row: two queries per lane -------------------------------------------
       const int j0 = row * kFlowRowQ + lane;
-      double qd[2][3];
-      float qf[2][3];
-      int sorig[2];
+      double qd[kFlowQ][3];
+      float qf[kFlowQ][3];
+      int sorig[kFlowQ];
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
+      for (int q = 0; q < kFlowQ; ++q) {
         const double2* s2 = reinterpret_cast<const double2*>(src64 + min(j0 + 32 * q, ns - 1));   // ragged tail: repeats
         const double2 a = __ldg(s2), b = __ldg(s2 + 1);
         sorig[q] = (int)__double_as_longlong(b.y);
@@ -555,15 +563,22 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
 #pragma unroll
         for (int a3 = 0; a3 < 3; ++a3) qf[q][a3] = (float)qd[q][a3];
       }
-      const float rlx = redux_minf(fminf(qf[0][0], qf[1][0])), rhx = redux_maxf(fmaxf(qf[0][0], qf[1][0]));
-      const float rly = redux_minf(fminf(qf[0][1], qf[1][1])), rhy = redux_maxf(fmaxf(qf[0][1], qf[1][1]));
-      const float rlz = redux_minf(fminf(qf[0][2], qf[1][2])), rhz = redux_maxf(fmaxf(qf[0][2], qf[1][2]));
-
-      f32x2 qxx[2], qyy[2], qzz[2];
-      float bestv[2], secondv[2], thr[2], a_bound[2], gbest[2][8];
-      int bestb[2];
+      float lo3[3], hi3[3];
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
+      for (int a3 = 0; a3 < 3; ++a3) {
+        lo3[a3] = hi3[a3] = qf[0][a3];
+#pragma unroll
+        for (int q = 1; q < kFlowQ; ++q) { lo3[a3] = fminf(lo3[a3], qf[q][a3]); hi3[a3] = fmaxf(hi3[a3], qf[q][a3]); }
+      }
+      const float rlx = redux_minf(lo3[0]), rhx = redux_maxf(hi3[0]);
+      const float rly = redux_minf(lo3[1]), rhy = redux_maxf(hi3[1]);
+      const float rlz = redux_minf(lo3[2]), rhz = redux_maxf(hi3[2]);
+
+      f32x2 qxx[kFlowQ], qyy[kFlowQ], qzz[kFlowQ];
+      float bestv[kFlowQ], secondv[kFlowQ], thr[kFlowQ], a_bound[kFlowQ], gbest[kFlowQ][8];
+      int bestb[kFlowQ];
+#pragma unroll
+      for (int q = 0; q < kFlowQ; ++q) {
         qxx[q] = pack2(qf[q][0], qf[q][0]); qyy[q] = pack2(qf[q][1], qf[q][1]); qzz[q] = pack2(qf[q][2], qf[q][2]);
         bestv[q] = secondv[q] = thr[q] = kInfF;
         bestb[q] = -1;
@@ -577,15 +592,15 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
           const float4 blo = __ldg(tg.box + 2 * b), bhi = __ldg(tg.box + 2 * b + 1);
           bool need = false;
 #pragma unroll
-          for (int q = 0; q < 2; ++q)
+          for (int q = 0; q < kFlowQ; ++q)
             need = need || !(box_lb3(qf[q][0], qf[q][1], qf[q][2], qf[q][0], qf[q][1], qf[q][2], blo, bhi) > thr[q]);
           if (!__any_sync(full, need)) return;
         }
-        tiles += 2u;
+        tiles += (unsigned)kFlowQ;
         const bool imp = flow_sweep_block(tg.t32, b, qxx, qyy, qzz, bestv, secondv, bestb, gbest);
         if (__any_sync(full, imp)) {
 #pragma unroll
-          for (int q = 0; q < 2; ++q) thr[q] = candidate_threshold(bestv[q], a_bound[q], 0.f);
+          for (int q = 0; q < kFlowQ; ++q) thr[q] = candidate_threshold(bestv[q], a_bound[q], 0.f);
         }
       };
       // phase A: the blocks whose box overlaps the row box (bound 0: they pass any threshold)
@@ -613,7 +628,11 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
           if (seed_block < tg.nblk) consider(seed_block);
         }
         // phase B: every other block within the largest candidate threshold of the row
-        float bound = redux_maxf(fmaxf(thr[0], thr[1]));
+        auto thr_max = [&]() { float m = thr[0];
+#pragma unroll
+          for (int q = 1; q < kFlowQ; ++q) m = fmaxf(m, thr[q]);
+          return m; };
+        float bound = redux_maxf(thr_max());
         for (int c0 = 0; c0 < tg.nblk; c0 += 32) {
           const int b = c0 + lane;
           const float lb = box_lb3(rlx, rly, rlz, rhx, rhy, rhz, __ldg(tg.box + 2 * b), __ldg(tg.box + 2 * b + 1));
@@ -624,15 +643,15 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
             m &= m - 1u;
             consider(bb);
           }
-          bound = redux_maxf(fmaxf(thr[0], thr[1]));
+          bound = redux_maxf(thr_max());
         }
       }
 
       // ---- exact resolution in float64 ----------------------------------------------------
-      int cpos[2], corig[2];
-      bool amb[2];
+      int cpos[kFlowQ], corig[kFlowQ];
+      bool amb[kFlowQ];
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
+      for (int q = 0; q < kFlowQ; ++q) {
         cpos[q] = -1; corig[q] = 0x7fffffff;
         amb[q] = !(secondv[q] > thr[q]);
         if (!amb[q]) {
@@ -660,7 +679,7 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
       }
       // rare: a second block is within the slack -> the warp scans all targets
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
+      for (int q = 0; q < kFlowQ; ++q) {
         unsigned vote = __ballot_sync(full, amb[q]);
         while (vote) {
           const int src_lane = __ffs((int)vote) - 1;
@@ -698,7 +717,7 @@ __global__ void __launch_bounds__(kFlowWarps * 32, 2) icp3d_flow_kernel(const Ru
       }
       // ---- float64 sums -------------------------------------------------------------------
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
+      for (int q = 0; q < kFlowQ; ++q) {
         if (j0 + 32 * q < ns) {
           const double2* m2 = reinterpret_cast<const double2*>(tg.t64 + cpos[q]);
           const double2 a = __ldg(m2), b = __ldg(m2 + 1);
