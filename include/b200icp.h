@@ -33,6 +33,7 @@ extern "C" {
 #define B200ICP_ERR_WORKSPACE (-3) /* workspace smaller than b200icp_workspace_bytes  */
 #define B200ICP_ERR_CUDA (-4)      /* launch failed; see cudaGetLastError             */
 #define B200ICP_ERR_NO_DEVICE (-5) /* no sm_100 device / wrong architecture           */
+#define B200ICP_ERR_BUSY (-7)      /* b200icp_submit_host_ranges: two calls are already in flight on this device */
 #define B200ICP_ERR_STATIC_SCRATCH (-6) /* b200icp_run_static: the problem needs more scratch than
                                            B200ICP_STATIC_SCRATCH_BYTES; use b200icp_run       */
 
@@ -276,6 +277,24 @@ int b200icp_run_pair_host(const double* src, int n_src, const double* tgt, int n
                           int normalize, double* T_out, double* err_out, int32_t* iters_out,
                           int32_t* status_out, int32_t* corr_out);
 int b200icp_host_release(void);
+
+/* b200icp_run_host_ranges in two halves, for a caller with several batches (several logs, a serving loop):
+ * b200icp_submit_host_ranges enqueues the uploads, the launch and the copies back and returns a ticket
+ * without waiting; b200icp_wait_host(ticket) returns once the outputs of that call are filled.  Up to TWO
+ * calls may be in flight per device (B200ICP_ERR_BUSY otherwise); each runs on an arena and streams of its
+ * own, so the upload and the first pairs of call k + 1 overlap the queue tail and the result copies of call
+ * k (a launch of 5 000 pairs ends with the SMs 13 % idle).  Every array passed in (inputs and
+ * outputs, and the exchange struct's pointers) must stay valid and untouched until the wait returns; use
+ * page-locked memory (below), or the copies are not asynchronous.  Results are those of the synchronous
+ * entry, bit for bit.  No counterpart in the reference (its loop is synchronous). */
+int b200icp_submit_host_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
+                               const double* sin_tab, double range_min, double range_max, double off_x, double off_y,
+                               const int32_t* pairs, const double* init, const double* epsilon,
+                               const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                               double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                               int32_t* corr_out, int32_t* counts_out, const b200icp_exchange* exchange,
+                               unsigned flags, int* ticket_out);
+int b200icp_wait_host(int ticket);
 
 /* Page-locked host memory for the arrays handed to the host entries (cudaHostAlloc / cudaFreeHost).
  * Optional: the host entries accept any host pointer, but copies from and to pageable memory are

@@ -48,6 +48,11 @@ SIGNATURES = {
                                         c_double, c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                         c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                         c_void_p, ctypes.c_uint]),
+    "b200icp_submit_host_ranges": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_double, c_double,
+                                        c_double, c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                        c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, ctypes.c_uint, ctypes.POINTER(c_int)]),
+    "b200icp_wait_host": (c_int, [c_int]),
     "b200icp_exchange_wait": (c_int, [c_void_p, c_int, ctypes.c_uint, c_int, c_void_p, c_void_p]),
     "b200icp_exchange_signal": (c_int, [c_void_p, c_void_p]),
     "b200icp_run_host": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -260,6 +260,7 @@ const char* b200icp_error_string(int code) {
     case B200ICP_ERR_WORKSPACE: return "workspace missing or smaller than b200icp_workspace_bytes";
     case B200ICP_ERR_CUDA: return "CUDA launch failed";
     case B200ICP_ERR_NO_DEVICE: return "no sm_100 (B200) device is current";
+    case B200ICP_ERR_BUSY: return "two submitted host calls are already in flight on this device; wait for one first";
     case B200ICP_ERR_STATIC_SCRATCH:
       return "b200icp_run_static: problem needs more scratch than B200ICP_STATIC_SCRATCH_BYTES (16 MiB); "
              "use b200icp_run with a caller workspace";

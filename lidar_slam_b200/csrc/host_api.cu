@@ -149,7 +149,11 @@ int download_results(HostArena& a, char* d, const SmallOffsets& o, const HostIo&
 }
 
 // ONE gated launch over the whole pair list while the pool arrives in slices (planar kernel).
-int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
+// gated_enqueue issues everything -- uploads, the launch, the copies back -- and returns without waiting;
+// gated_finish waits for the copy stream and reports.  run_gated = both (the synchronous entries);
+// b200icp_submit_host_ranges / b200icp_wait_host call them apart, on arenas of their own.
+int gated_enqueue(HostArena& a, const HostPool& pool, const HostIo& io, int* rc_run_out) {
+  *rc_run_out = B200ICP_OK;
   Carver cv;
   const size_t row_bytes = pool.row_bytes();
   const size_t o_pool = cv.take((size_t)pool.n_scans * row_bytes);
@@ -163,6 +167,7 @@ int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
   const size_t o_ws = cv.take(ws_bytes);
   if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
   char* d = a.base;
+  a.progress_host[kMaxSlices - 1] = 0u;
   B200_TRY(cudaMemsetAsync(d + o_flag, 0, 256, a.copy));
   if (pool.kind == 0) {
     B200_TRY(cudaMemcpyAsync(d + o_counts, pool.counts, (size_t)pool.n_scans * 4, cudaMemcpyHostToDevice, a.copy));
@@ -238,9 +243,21 @@ int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
     B200_TRY(cudaMemcpyAsync(a.progress_host + kMaxSlices - 1, d + o_ws + 20, sizeof(unsigned int),
                              cudaMemcpyDeviceToHost, a.copy));
   }
+  *rc_run_out = rc_run;
+  return B200ICP_OK;
+}
+
+int gated_finish(HostArena& a, int rc_run) {
   B200_TRY(cudaStreamSynchronize(a.copy));
   if (rc_run == B200ICP_OK && a.progress_host[kMaxSlices - 1] != 0u) return B200ICP_ERR_CUDA;
   return rc_run;
+}
+
+int run_gated(HostArena& a, const HostPool& pool, const HostIo& io) {
+  int rc_run = B200ICP_OK;
+  const int rc = gated_enqueue(a, pool, io, &rc_run);
+  if (rc != B200ICP_OK) { cudaStreamSynchronize(a.copy); cudaGetLastError(); return rc; }
+  return gated_finish(a, rc_run);
 }
 
 // Chunks of the pair list on two compute streams; each chunk waits for the pool prefix it references.
@@ -407,6 +424,68 @@ int b200icp_run_host_ranges(const void* ranges, int ranges_dtype, int n_scans, i
   return run_host_impl(pool, io);
 }
 
+// ---- two calls in flight: submit / wait ---------------------------------------------------------------
+// Lanes 0 and 1 of a device have arenas, streams and pinned words of their own (beside the arena of the
+// synchronous entries), so the uploads and the head of call k + 1 run under the queue tail and the copies
+// back of call k.
+namespace {
+struct Lane { HostArena arena; bool busy = false; int rc_run = B200ICP_OK; unsigned gen = 0; };
+Lane g_lane[64][2];
+}  // namespace
+
+int b200icp_submit_host_ranges(const void* ranges, int ranges_dtype, int n_scans, int n_beams, const double* cos_tab,
+                               const double* sin_tab, double range_min, double range_max, double off_x, double off_y,
+                               const int32_t* pairs, const double* init, const double* epsilon,
+                               const uint8_t* normalize, int n_pairs, int max_iters, double stopping_thresh,
+                               double* T_out, double* err_out, int32_t* iters_out, int32_t* status_out,
+                               int32_t* corr_out, int32_t* counts_out, const b200icp_exchange* exchange,
+                               unsigned flags, int* ticket_out) {
+  if (!ticket_out) return B200ICP_ERR_BAD_ARG;
+  *ticket_out = -1;
+  if (!ranges || !cos_tab || !sin_tab || n_beams <= 0 || n_beams > kMax2dPoints || (ranges_dtype != 0 && ranges_dtype != 1) ||
+      !pairs || !init || !epsilon || !normalize || !T_out || n_scans <= 0 || n_pairs <= 0 || max_iters < 0)
+    return B200ICP_ERR_BAD_ARG;
+  HostPool pool{};
+  pool.data = ranges; pool.kind = ranges_dtype ? 2 : 1; pool.n_scans = n_scans; pool.n_beams = n_beams;
+  pool.n_max = n_beams + (n_beams & 1); pool.dim = 2;
+  pool.cos_tab = cos_tab; pool.sin_tab = sin_tab; pool.range_min = range_min; pool.range_max = range_max;
+  pool.off_x = off_x; pool.off_y = off_y; pool.counts_out = counts_out;
+  HostIo io{pairs, init, epsilon, normalize, n_pairs, max_iters, stopping_thresh, T_out, err_out, iters_out,
+            status_out, corr_out, exchange, flags | b200icp::env_flags()};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return B200ICP_ERR_NO_DEVICE; }
+  std::lock_guard<std::mutex> lock(g_mutex);
+  int which = -1;
+  for (int k = 0; k < 2; ++k)
+    if (!g_lane[dev][k].busy) { which = k; break; }
+  if (which < 0) return B200ICP_ERR_BUSY;
+  Lane& ln = g_lane[dev][which];
+  if (!arena_init(ln.arena)) { cudaGetLastError(); return B200ICP_ERR_CUDA; }
+  int rc_run = B200ICP_OK;
+  const int rc = gated_enqueue(ln.arena, pool, io, &rc_run);
+  if (rc != B200ICP_OK) { cudaStreamSynchronize(ln.arena.copy); cudaGetLastError(); return rc; }
+  ln.busy = true; ln.rc_run = rc_run; ln.gen = (ln.gen + 1u) & 0x7fffffu;
+  *ticket_out = (int)((ln.gen << 8) | ((unsigned)dev << 1) | (unsigned)which);
+  return B200ICP_OK;
+}
+
+int b200icp_wait_host(int ticket) {
+  if (ticket < 0) return B200ICP_ERR_BAD_ARG;
+  const int which = ticket & 1, dev = (ticket >> 1) & 63;
+  const unsigned gen = (unsigned)ticket >> 8;
+  Lane& ln = g_lane[dev][which];
+  int rc_run;
+  {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    if (!ln.busy || ln.gen != gen) return B200ICP_ERR_BAD_ARG;      // unknown, or already waited for
+    rc_run = ln.rc_run;
+  }
+  const int rc = gated_finish(ln.arena, rc_run);     // outside the lock: the other lane may be submitted meanwhile
+  std::lock_guard<std::mutex> lock(g_mutex);
+  ln.busy = false;
+  return rc;
+}
+
 // run_icp for ONE pair, host arrays in and out: the un-batched drop-in (modules/icp.py:123-189 as
 // modules/localization.py:120 calls it).  Everything the launch needs travels in ONE pinned block
 // and one host-to-device copy, everything it returns in one device-to-host copy.
@@ -505,6 +584,10 @@ int b200icp_host_release(void) {
   std::lock_guard<std::mutex> lock(g_mutex);
   HostArena& a = g_arena[dev];
   if (a.base) { cudaFree(a.base); a.base = nullptr; a.cap = 0; }
+  for (int k = 0; k < 2; ++k) {                       // the lanes of submit / wait, unless a call is in flight on them
+    Lane& ln = g_lane[dev][k];
+    if (!ln.busy && ln.arena.base) { cudaFree(ln.arena.base); ln.arena.base = nullptr; ln.arena.cap = 0; }
+  }
   return B200ICP_OK;
 }
 

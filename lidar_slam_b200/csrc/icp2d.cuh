@@ -273,6 +273,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     fence_mbar_init();
   }
   uint32_t parity = 0;
+  unsigned retired = 0;   // pairs this thread (tid 0) has retired, announced to the peers when the CTA leaves the queue
   PHASE_DECL
 
   for (;;) {
@@ -308,7 +309,10 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
     }
     __syncthreads();
     const int pair = s_pair[0];
-    if (pair >= p.n_pairs) break;
+    if (pair >= p.n_pairs) {
+      if (tid == 0) pairs_retired(p, p.queue + 6, retired);    // this CTA's pairs, announced once
+      break;
+    }
 
     const int si = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
     int early = -1;
@@ -345,7 +349,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           const double* T0 = p.init + (size_t)pair * 16;
           store_pose_to_peers(p, pair, T0[3], T0[7], T0[0], T0[4], __longlong_as_double(0x7ff8000000000000LL));
         }
-        pair_retired(p, p.queue + 6);
+        ++retired;
       }
       if (p.corr_out)
         for (int j = tid; j < p.n_max; j += W * 32) p.corr_out[(size_t)pair * p.n_max + j] = -1;
@@ -847,7 +851,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_kernel(const RunParams p) 
           if (p.iters_out) p.iters_out[pair] = passes;
           if (p.status_out) p.status_out[pair] = status;
           store_pose_to_peers(p, pair, tx, ty, r00, r10, err);
-          pair_retired(p, p.queue + 6);
+          ++retired;
         }
         if (p.corr_out) {
           int* out = p.corr_out + (size_t)pair * p.n_max;

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
     fence_mbar_init();
   }
   uint32_t parity = 0;
+  unsigned retired = 0;   // pairs this thread (tid 0) has retired, announced to the peers when the CTA leaves the queue
 
   for (;;) {
     __syncthreads();  // previous pair fully consumed; mbarrier initialised
@@ -171,7 +172,10 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
     }
     __syncthreads();
     const int pair = s_ctl[0];
-    if (pair >= p.n_pairs) break;
+    if (pair >= p.n_pairs) {
+      if (tid == 0) pairs_retired(p, p.queue + 6, retired);    // this CTA's pairs, announced once
+      break;
+    }
 
     const int si = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
     int early = -1;
@@ -308,7 +312,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
           const double* T0 = p.init + (size_t)pair * 16;
           store_pose_to_peers(p, pair, T0[3], T0[7], T0[0], T0[4], kNaN);
         }
-        pair_retired(p, p.queue + 6);
+        ++retired;
       }
       if (p.corr_out)
         for (int j = tid; j < p.n_max; j += W * 32) p.corr_out[(size_t)pair * p.n_max + j] = -1;
@@ -650,7 +654,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
           if (p.iters_out) p.iters_out[pair] = passes;
           if (p.status_out) p.status_out[pair] = status;
           store_pose_to_peers(p, pair, tx, ty, r00, r10, err);
-          pair_retired(p, p.queue + 6);
+          ++retired;
         }
         if (p.corr_out) {
           // every lane wrote the matches of its own rows; the barrier of the exchange above made

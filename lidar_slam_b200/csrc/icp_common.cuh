@@ -275,12 +275,15 @@ __device__ __forceinline__ void raise_arrival_flags(const RunParams& p) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(p.flag_val) : "memory");
   }
 }
-// called by the one thread that has just written pair results (and stored its row to the peers):
-// counts retired pairs; the last one announces the launch to every rank
-__device__ __forceinline__ void pair_retired(const RunParams& p, unsigned* counter) {
-  if (p.n_peers <= 0 || p.flag_off == 0) return;
+// Pairs retired by ONE thread of a CTA (the thread that wrote their results and stored their rows to the
+// peers), announced together when the CTA leaves the work queue: one system-scope fence per CTA instead of
+// one per pair (a fence waits for the acknowledgement of every peer store over NVLink; per pair it cost
+// 29 us per 4955-pair launch at 2 GPUs, profiles/r2c_*).  The CTA whose count completes the launch
+// announces it to every rank.
+__device__ __forceinline__ void pairs_retired(const RunParams& p, unsigned* counter, unsigned count) {
+  if (p.n_peers <= 0 || p.flag_off == 0 || count == 0u) return;
   __threadfence_system();
-  if (atomicAdd(counter, 1u) == (unsigned)(p.n_pairs - 1)) raise_arrival_flags(p);
+  if (atomicAdd(counter, count) + count == (unsigned)p.n_pairs) raise_arrival_flags(p);
 }
 
 }  // namespace b200icp

@@ -217,6 +217,59 @@ def run_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms=N
     return HostBatchResult(o.T, o.err, o.iters, o.status, o.corr if return_correspondences else None), o.counts
 
 
+class HostTicket:
+    """A submitted run_icp_ranges_host call (b200icp_submit_host_ranges): `wait()` returns what the
+    synchronous call returns.  Holds every array the library still reads or writes."""
+
+    def __init__(self, ticket: int, out: HostRangesWorkspace, want_corr: bool, keep):
+        self._ticket, self._out, self._want_corr, self._keep = ticket, out, want_corr, keep
+
+    def wait(self):
+        if self._ticket is not None:
+            t, self._ticket = self._ticket, None
+            _lib.check(_lib.load().b200icp_wait_host(t), "b200icp_wait_host")
+            self._keep = None
+        o = self._out
+        return HostBatchResult(o.T, o.err, o.iters, o.status, o.corr if self._want_corr else None), o.counts
+
+
+def submit_icp_ranges_host(ranges: np.ndarray, pairs: np.ndarray, init_transforms, out: HostRangesWorkspace,
+                           epsilon=0.01, max_iters: int = 2000, stopping_thresh: float = 1e-4, normalize_error=False,
+                           return_correspondences: bool = False, range_min: float = 0.1, range_max: float = 30.0,
+                           offset_xy=(0.13323, 0.0), flags: int = 0, peer_pose_ptrs=None, peer_row0: int = 0,
+                           peer_flag=None) -> HostTicket:
+    """run_icp_ranges_host without the wait: returns a HostTicket at once; up to two calls may be in flight
+    per device, each with a HostRangesWorkspace of its own (`out`, required: the results land there).  The
+    upload and the first pairs of the next call overlap the queue tail and the result copies of this one.
+    `ranges`, `pairs` and `init_transforms` must be C-contiguous arrays of the right dtype (float64 / float32,
+    int32, float64) -- ideally page-locked (pinned_empty) -- and must not be modified before `wait()`."""
+    lib = _lib.load()
+    if ranges.dtype not in (np.float64, np.float32) or not ranges.flags.c_contiguous or ranges.ndim != 2 \
+            or ranges.shape[1] == 0 or ranges.shape[1] > 2048:
+        raise ValueError("ranges must be a C-contiguous float64/float32 [S, n_beams] array with n_beams <= 2048")
+    n_scans, n_beams = ranges.shape
+    n_max = n_beams + (n_beams & 1)
+    if pairs.dtype != np.int32 or not pairs.flags.c_contiguous or pairs.ndim != 2 or pairs.shape[1] != 2:
+        raise ValueError("pairs must be a C-contiguous int32 [B, 2] array")
+    n_pairs = pairs.shape[0]
+    init = init_transforms
+    if init.dtype != np.float64 or not init.flags.c_contiguous or init.shape != (n_pairs, 4, 4):
+        raise ValueError("init_transforms must be a C-contiguous float64 [B, 4, 4] array")
+    if out.T.shape[0] != n_pairs or out.counts.shape[0] != n_scans or (return_correspondences and out.corr is None):
+        raise ValueError("`out` was built for another batch shape")
+    cos_t, sin_t = out.beam_tables(n_beams)
+    eps, norm = out.per_pair(epsilon, normalize_error)
+    ex, keep = _lib.make_exchange(peer_pose_ptrs, peer_row0, *(peer_flag or (0, 0, 0)))
+    ticket = ctypes.c_int(-1)
+    _lib.check(lib.b200icp_submit_host_ranges(
+        _p(ranges), 1 if ranges.dtype == np.float32 else 0, n_scans, n_beams, _p(cos_t), _p(sin_t), float(range_min),
+        float(range_max), float(offset_xy[0]), float(offset_xy[1]), _p(pairs), _p(init), _p(eps), _p(norm), n_pairs,
+        int(max_iters), float(stopping_thresh), _p(out.T), _p(out.err), _p(out.iters), _p(out.status),
+        _p(out.corr) if return_correspondences else None, _p(out.counts),
+        None if ex is None else ctypes.byref(ex), int(flags), ctypes.byref(ticket)), "b200icp_submit_host_ranges")
+    return HostTicket(ticket.value, out, return_correspondences, (ranges, pairs, init, eps, norm, cos_t, sin_t, ex, keep))
+
+
 def release() -> None:
     """Free the library's device arena on the current device."""
     _lib.check(_lib.load().b200icp_host_release(), "b200icp_host_release")

@@ -111,3 +111,46 @@ def test_gated_launch_gives_up_with_status_not_resident():
     assert torch.equal(T[~torch.from_numpy(resident).cuda()], b["init"][~torch.from_numpy(resident).cuda()])
     assert bool(torch.isnan(err[~torch.from_numpy(resident).cuda()]).all())
     assert int(ws[20:24].cpu().numpy().view(np.uint32)[0]) == 1
+
+
+def test_two_submitted_calls_in_flight_equal_the_synchronous_entry():
+    """b200icp_submit_host_ranges / b200icp_wait_host: two batches in flight on one device, waited for in
+    either order, fill their own workspaces with the bits of the synchronous entry; a third submit is
+    refused (BUSY) and a ticket cannot be waited for twice."""
+    from lidar_slam_b200 import _lib, hostapi, synth
+    batches = []
+    for seed in (51, 52, 53):
+        b = synth.odometry_batch(2300, seed=seed, device="cpu", with_ranges=True)
+        r = hostapi.pinned_empty(tuple(b["ranges"].shape), np.float64); r[:] = b["ranges"].numpy()
+        p = hostapi.pinned_empty((2300, 2), np.int32); p[:] = b["pairs"].numpy()
+        i = hostapi.pinned_empty((2300, 4, 4), np.float64); i[:] = b["init"].numpy()
+        batches.append((r, p, i))
+    n_scans, n_beams = batches[0][0].shape
+    want = []
+    for r, p, i in batches:
+        res, counts = hostapi.run_icp_ranges_host(r, p, i, epsilon=1e-3, return_correspondences=True)
+        want.append((res.T.copy(), res.error.copy(), res.iters.copy(), res.correspondences.copy(), counts.copy()))
+    ws = [hostapi.HostRangesWorkspace(2300, n_scans, n_beams + (n_beams & 1), True) for _ in range(2)]
+    for order in ((0, 1), (1, 0)):
+        for w in ws:
+            w.T.fill(np.nan); w.iters.fill(-7)
+        t = [hostapi.submit_icp_ranges_host(*batches[k], ws[k], epsilon=1e-3, return_correspondences=True) for k in range(2)]
+        with pytest.raises(RuntimeError, match="in flight"):
+            hostapi.submit_icp_ranges_host(*batches[2], ws[0], epsilon=1e-3)
+        for k in order:
+            res, counts = t[k].wait()
+            T, err, iters, corr, cnt = want[k]
+            assert np.array_equal(res.T, T) and np.array_equal(res.error, err) and np.array_equal(res.iters, iters)
+            assert np.array_equal(res.correspondences, corr) and np.array_equal(counts, cnt)
+    # a pipeline: submit k + 1, then wait for k
+    tickets = [None, None]
+    for step in range(5):
+        k = step % 2
+        if tickets[k] is not None:
+            tickets[k].wait()
+        tickets[k] = hostapi.submit_icp_ranges_host(*batches[step % 3], ws[k], epsilon=1e-3, return_correspondences=True)
+    res4, _ = tickets[0].wait()           # step 4 -> batch 1
+    res3, _ = tickets[1].wait()           # step 3 -> batch 0
+    assert np.array_equal(res4.T, want[1][0]) and np.array_equal(res3.T, want[0][0])
+    lib = _lib.load()
+    assert lib.b200icp_wait_host(12345 << 8) == -1          # unknown ticket
