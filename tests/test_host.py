@@ -37,6 +37,44 @@ def test_product_path_fails_loudly_without_gpu():
         eng.run_icp(np.zeros((5, 2)), np.ones((5, 2)))
 
 
+def test_host_entries_validate_before_touching_the_device_and_fail_loudly_without_one():
+    """hostapi: page-locked buffers fall back to pageable ones when cudaHostAlloc is unavailable, the
+    submit wrapper rejects arrays the library could not read asynchronously, and without a GPU every
+    entry raises (no CPU fallback); run_static reports its size limit without a device, too."""
+    from lidar_slam_b200 import _lib, hostapi
+    a = hostapi.pinned_empty((7, 3), np.float32)
+    assert a.shape == (7, 3) and a.dtype == np.float32 and a.flags.c_contiguous
+    a[:] = 1.5
+    ws = hostapi.HostRangesWorkspace(4, 5, 1082)
+    assert ws.T.shape == (4, 4, 4) and ws.counts.shape == (5,)
+    c, s_ = ws.beam_tables(1081)
+    c0, s0 = hostapi.beam_tables(1081)
+    assert np.array_equal(c, c0) and np.array_equal(s_, s0)
+    eps, norm = ws.per_pair(1e-3, True)
+    assert eps.shape == (4,) and float(eps[2]) == 1e-3 and norm.dtype == np.uint8 and int(norm[3]) == 1
+    ranges = np.full((5, 1081), 4.0)
+    pairs = np.array([[1, 0], [2, 1], [3, 2], [4, 3]], np.int32)
+    init = np.broadcast_to(np.eye(4), (4, 4, 4)).copy()
+    with pytest.raises(ValueError, match="pairs"):
+        hostapi.submit_icp_ranges_host(ranges, pairs.astype(np.int64), init, ws)
+    with pytest.raises(ValueError, match="ranges"):
+        hostapi.submit_icp_ranges_host(ranges[:, ::2], pairs, init, ws)
+    with pytest.raises(ValueError, match="another batch shape"):
+        hostapi.submit_icp_ranges_host(ranges, pairs[:3].copy(), init[:3].copy(), ws)
+    lib = _lib.load()
+    assert lib.b200icp_wait_host(-1) == -1 and lib.b200icp_wait_host(5 << 8) == -1
+    assert b"in flight" in lib.b200icp_error_string(-7)
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            hostapi.submit_icp_ranges_host(ranges, pairs, init, ws)
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            hostapi.run_icp_ranges_host(ranges, pairs, init)
+        # the size limit of the allocation-free entry is checked before the device is
+        vp = ctypes.c_void_p
+        assert lib.b200icp_run_static(vp(8), vp(8), 2, 20000, 3, vp(8), vp(8), vp(8), vp(8), 512, 10, 1e-4,
+                                      vp(8), None, None, None, None, None) == _lib.ERR_STATIC_SCRATCH
+
+
 def test_product_never_imports_oracle():
     pkg = os.path.join(ROOT, "lidar_slam_b200")
     for dirpath, _, files in os.walk(pkg):
