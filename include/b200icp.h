@@ -68,6 +68,8 @@ extern "C" {
                                           (1e-13), not bit for bit; b200icp_run_pair_host sets it.    */
 #define B200ICP_FLAG_HOST_CHUNKED 0x2u /* host entries: pair chunks alternating on two streams
                                           instead of ONE gated launch (A/B)                     */
+#define B200ICP_FLAG_HOST_NO_DIRECT 0x10u /* host entries: always copy the results back; by default a result
+                                             array in page-locked memory is written by the kernel itself */
 #define B200ICP_FLAG_SLICES(n) (((unsigned)(n)&0xffu) << 8)  /* host entries: pool slices (0 = 24) */
 #define B200ICP_FLAG_CHUNKS(n) (((unsigned)(n)&0xffu) << 16) /* chunked host path: chunks (0 = 6)  */
 

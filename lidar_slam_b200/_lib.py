@@ -90,6 +90,7 @@ FLAG_EXHAUSTIVE = 0x1
 FLAG_HOST_CHUNKED = 0x2
 FLAG_NO_PRUNE = 0x4
 FLAG_LATENCY = 0x8
+FLAG_HOST_NO_DIRECT = 0x10
 
 
 def flag_slices(n: int) -> int:

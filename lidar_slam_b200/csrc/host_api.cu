@@ -130,6 +130,21 @@ SmallOffsets carve_small(Carver& cv, const HostIo& io, int n_max) {
   return o;
 }
 
+// Page-locked host memory is mapped into the device's address space (unified addressing): a small result
+// array there can be the kernel's output pointer itself, so that the results leave the device as pairs
+// retire instead of in a train of small copies behind the launch (each costs 6-8 us of latency; T, error,
+// passes, status and counts: ~45 us of a 2 ms call).  Returns nullptr for pageable memory.
+void* device_view_of_pinned(const void* host_ptr) {
+  if (!host_ptr) return nullptr;
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, host_ptr) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  if (at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
+  return at.devicePointer;
+}
+
+struct DirectOut { double* T = nullptr; double* err = nullptr; int32_t* iters = nullptr; int32_t* status = nullptr;
+                   int32_t* counts = nullptr; };
+
 int upload_small(HostArena& a, char* d, const SmallOffsets& o, const HostIo& io) {
   B200_TRY(cudaMemcpyAsync(d + o.pairs, io.pairs, (size_t)io.n_pairs * 8, cudaMemcpyHostToDevice, a.copy));
   B200_TRY(cudaMemcpyAsync(d + o.init, io.init, (size_t)io.n_pairs * 128, cudaMemcpyHostToDevice, a.copy));
@@ -138,12 +153,13 @@ int upload_small(HostArena& a, char* d, const SmallOffsets& o, const HostIo& io)
   return B200ICP_OK;
 }
 
-int download_results(HostArena& a, char* d, const SmallOffsets& o, const HostIo& io, int n_max) {
+int download_results(HostArena& a, char* d, const SmallOffsets& o, const HostIo& io, int n_max,
+                     const DirectOut& direct = DirectOut()) {
   const size_t n = (size_t)io.n_pairs;
-  B200_TRY(cudaMemcpyAsync(io.T_out, d + o.T, n * 128, cudaMemcpyDeviceToHost, a.copy));
-  if (io.err_out) B200_TRY(cudaMemcpyAsync(io.err_out, d + o.err, n * 8, cudaMemcpyDeviceToHost, a.copy));
-  if (io.iters_out) B200_TRY(cudaMemcpyAsync(io.iters_out, d + o.iters, n * 4, cudaMemcpyDeviceToHost, a.copy));
-  if (io.status_out) B200_TRY(cudaMemcpyAsync(io.status_out, d + o.status, n * 4, cudaMemcpyDeviceToHost, a.copy));
+  if (!direct.T) B200_TRY(cudaMemcpyAsync(io.T_out, d + o.T, n * 128, cudaMemcpyDeviceToHost, a.copy));
+  if (io.err_out && !direct.err) B200_TRY(cudaMemcpyAsync(io.err_out, d + o.err, n * 8, cudaMemcpyDeviceToHost, a.copy));
+  if (io.iters_out && !direct.iters) B200_TRY(cudaMemcpyAsync(io.iters_out, d + o.iters, n * 4, cudaMemcpyDeviceToHost, a.copy));
+  if (io.status_out && !direct.status) B200_TRY(cudaMemcpyAsync(io.status_out, d + o.status, n * 4, cudaMemcpyDeviceToHost, a.copy));
   if (io.corr_out) B200_TRY(cudaMemcpyAsync(io.corr_out, d + o.corr, n * n_max * 4, cudaMemcpyDeviceToHost, a.copy));
   return B200ICP_OK;
 }
@@ -168,6 +184,14 @@ int gated_enqueue(HostArena& a, const HostPool& pool, const HostIo& io, int* rc_
   if (!arena_reserve(a, cv.o)) return B200ICP_ERR_CUDA;
   char* d = a.base;
   a.progress_host[kMaxSlices - 1] = 0u;
+  DirectOut direct;
+  if (!(io.flags & B200ICP_FLAG_HOST_NO_DIRECT)) {
+    direct.T = static_cast<double*>(device_view_of_pinned(io.T_out));
+    direct.err = static_cast<double*>(device_view_of_pinned(io.err_out));
+    direct.iters = static_cast<int32_t*>(device_view_of_pinned(io.iters_out));
+    direct.status = static_cast<int32_t*>(device_view_of_pinned(io.status_out));
+    if (pool.kind) direct.counts = static_cast<int32_t*>(device_view_of_pinned(pool.counts_out));
+  }
   B200_TRY(cudaMemsetAsync(d + o_flag, 0, 256, a.copy));
   if (pool.kind == 0) {
     B200_TRY(cudaMemcpyAsync(d + o_counts, pool.counts, (size_t)pool.n_scans * 4, cudaMemcpyHostToDevice, a.copy));
@@ -175,7 +199,8 @@ int gated_enqueue(HostArena& a, const HostPool& pool, const HostIo& io, int* rc_
     B200_TRY(cudaMemcpyAsync(d + o_tabs, pool.cos_tab, (size_t)pool.n_beams * 8, cudaMemcpyHostToDevice, a.copy));
     B200_TRY(cudaMemcpyAsync(d + o_tabs + (size_t)pool.n_beams * 8, pool.sin_tab, (size_t)pool.n_beams * 8,
                              cudaMemcpyHostToDevice, a.copy));
-    if (pool.counts_out) B200_TRY(cudaMemsetAsync(d + o_counts, 0xff, (size_t)pool.n_scans * 4, a.copy));   // -1: not referenced
+    if (direct.counts) memset(pool.counts_out, 0xff, (size_t)pool.n_scans * 4);                          // -1: not referenced
+    else if (pool.counts_out) B200_TRY(cudaMemsetAsync(d + o_counts, 0xff, (size_t)pool.n_scans * 4, a.copy));
   }
   const int rc_up = upload_small(a, d, o, io);
   if (rc_up != B200ICP_OK) return rc_up;
@@ -216,8 +241,10 @@ int gated_enqueue(HostArena& a, const HostPool& pool, const HostIo& io, int* rc_
         reinterpret_cast<const double*>(d + o_pool), reinterpret_cast<const int32_t*>(d + o_counts), pool.n_scans,
         pool.n_max, 2, reinterpret_cast<const int32_t*>(d + o.pairs), reinterpret_cast<const double*>(d + o.init),
         reinterpret_cast<const double*>(d + o.eps), reinterpret_cast<const uint8_t*>(d + o.norm), io.n_pairs,
-        io.max_iters, io.stopping_thresh, reinterpret_cast<double*>(d + o.T), reinterpret_cast<double*>(d + o.err),
-        reinterpret_cast<int32_t*>(d + o.iters), reinterpret_cast<int32_t*>(d + o.status),
+        io.max_iters, io.stopping_thresh, direct.T ? direct.T : reinterpret_cast<double*>(d + o.T),
+        direct.err ? direct.err : reinterpret_cast<double*>(d + o.err),
+        direct.iters ? direct.iters : reinterpret_cast<int32_t*>(d + o.iters),
+        direct.status ? direct.status : reinterpret_cast<int32_t*>(d + o.status),
         io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) : nullptr, d + o_ws, ws_bytes, a.comp[0],
         reinterpret_cast<const unsigned int*>(d + o_flag), io.exchange, io.flags);
   } else {
@@ -226,18 +253,20 @@ int gated_enqueue(HostArena& a, const HostPool& pool, const HostIo& io, int* rc_
         reinterpret_cast<const double*>(d + o_tabs) + pool.n_beams, pool.range_min, pool.range_max, pool.off_x,
         pool.off_y, reinterpret_cast<const int32_t*>(d + o.pairs), reinterpret_cast<const double*>(d + o.init),
         reinterpret_cast<const double*>(d + o.eps), reinterpret_cast<const uint8_t*>(d + o.norm), io.n_pairs,
-        io.max_iters, io.stopping_thresh, reinterpret_cast<double*>(d + o.T), reinterpret_cast<double*>(d + o.err),
-        reinterpret_cast<int32_t*>(d + o.iters), reinterpret_cast<int32_t*>(d + o.status),
+        io.max_iters, io.stopping_thresh, direct.T ? direct.T : reinterpret_cast<double*>(d + o.T),
+        direct.err ? direct.err : reinterpret_cast<double*>(d + o.err),
+        direct.iters ? direct.iters : reinterpret_cast<int32_t*>(d + o.iters),
+        direct.status ? direct.status : reinterpret_cast<int32_t*>(d + o.status),
         io.corr_out ? reinterpret_cast<int32_t*>(d + o.corr) : nullptr,
-        pool.counts_out ? reinterpret_cast<int32_t*>(d + o_counts) : nullptr, d + o_ws, ws_bytes, a.comp[0],
+        direct.counts ? direct.counts : (pool.counts_out ? reinterpret_cast<int32_t*>(d + o_counts) : nullptr), d + o_ws, ws_bytes, a.comp[0],
         reinterpret_cast<const unsigned int*>(d + o_flag), io.exchange, io.flags);
   }
   B200_TRY(cudaEventRecord(a.done[0], a.comp[0]));
   B200_TRY(cudaStreamWaitEvent(a.copy, a.done[0], 0));
   if (rc_run == B200ICP_OK) {
-    const int rc_dn = download_results(a, d, o, io, pool.n_max);
+    const int rc_dn = download_results(a, d, o, io, pool.n_max, direct);
     if (rc_dn != B200ICP_OK) return rc_dn;
-    if (pool.kind && pool.counts_out)
+    if (pool.kind && pool.counts_out && !direct.counts)
       B200_TRY(cudaMemcpyAsync(pool.counts_out, d + o_counts, (size_t)pool.n_scans * 4, cudaMemcpyDeviceToHost, a.copy));
     // workspace word 5: the kernel gave up waiting for the pool (never expected; those pairs were not run)
     B200_TRY(cudaMemcpyAsync(a.progress_host + kMaxSlices - 1, d + o_ws + 20, sizeof(unsigned int),

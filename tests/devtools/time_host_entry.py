@@ -33,8 +33,8 @@ for _ in range(10):
 ev[1].record(); torch.cuda.synchronize()
 ms_copy = ev[0].elapsed_time(ev[1]) / 10
 print(f"upload alone: {ranges.nbytes / 1e6:.1f} MB in {ms_copy:.3f} ms = {ranges.nbytes / ms_copy / 1e6:.1f} GB/s")
-for slices in (0, 4, 8, 12, 16, 24, 32):
-    fl = _lib.flag_slices(slices) if slices else 0
+for slices, direct in ((0, True), (0, False), (8, True), (16, True), (16, False), (24, True), (32, True)):
+    fl = (_lib.flag_slices(slices) if slices else 0) | (0 if direct else _lib.FLAG_HOST_NO_DIRECT)
     best, tot = 1e9, 0.0
     for rep in range(14):
         t0 = time.perf_counter()
@@ -42,4 +42,4 @@ for slices in (0, 4, 8, 12, 16, 24, 32):
         dt = (time.perf_counter() - t0) * 1e3
         if rep >= 4:
             best, tot = min(best, dt), tot + dt
-    print(f"slices {slices or 'default'}: best {best:.3f} ms  mean {tot / 10:.3f} ms  {n / (tot / 10) * 1e3:.0f} pairs/s")
+    print(f"slices {slices or 'default'}{'' if direct else ' (results copied back)'}: best {best:.3f} ms  mean {tot / 10:.3f} ms  {n / (tot / 10) * 1e3:.0f} pairs/s")
