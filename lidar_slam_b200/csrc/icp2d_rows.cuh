@@ -436,15 +436,32 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
 #pragma unroll 1
         for (int phase = 0;; ++phase) {
           done_lo |= m_lo; done_hi |= m_hi;
-          tiles += (unsigned)(R * (__popc(m_lo) + __popc(m_hi)));
+          // A block admitted by the ROW's bound (phase 1: it does not overlap the row box) is swept only if
+          // at least one lane's OWN point-to-box bound is within that lane's threshold: the bound is the
+          // candidate arithmetic on a degenerate box, so a block refused here holds no target with
+          // d32 <= thr(q) for any query of the row -- typically the neighbours of the overlapping blocks,
+          // which only the queries at the end of the row can reach.
+          auto admitted = [&](int b) -> bool {
+            if (!PRUNE || phase == 0) return true;
+            const float4 box = bb[b];
+            bool need = false;
+#pragma unroll
+            for (int q = 0; q < R; ++q)
+              need = need || !(box_lb(make_float4(fqx[q], fqx[q], fqy[q], fqy[q]), box) > thr[q]);
+            return __any_sync(full, need);
+          };
           while (m_lo) {
             const int b = __ffs((int)m_lo) - 1;
             m_lo &= m_lo - 1u;
+            if (!admitted(b)) continue;
+            tiles += (unsigned)R;
             sweep_block_rows<R>(tp, b, qxx, qyy, best, second, gbest);
           }
           while (m_hi) {
             const int b = 32 + __ffs((int)m_hi) - 1;
             m_hi &= m_hi - 1u;
+            if (!admitted(b)) continue;
+            tiles += (unsigned)R;
             sweep_block_rows<R>(tp, b, qxx, qyy, best, second, gbest);
           }
           // the threshold the resolution uses (final once no further block is swept)
