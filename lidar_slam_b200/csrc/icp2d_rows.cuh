@@ -59,7 +59,9 @@ __host__ __device__ inline Rows2dLayout rows2d_layout(int n_max, int warps, bool
 // One 32-target block against the R queries of every lane.  The eight group-of-four minima of a
 // query's new best block are kept (gbest) so that the resolution can tell which groups hold
 // candidates without evaluating the block a second time.
-template <int R>
+// FIRST: the first block a row sweeps -- it becomes the best block unconditionally (best = second = "none"
+// before it), so the words and the group minima are written instead of compared and selected.
+template <int R, bool FIRST = false>
 __device__ __forceinline__ void sweep_block_rows(const ulonglong2* tp, int b, const f32x2 (&qxx)[R],
                                                  const f32x2 (&qyy)[R], unsigned (&best)[R],
                                                  unsigned (&second)[R], float (&gbest)[R][8]) {
@@ -86,12 +88,19 @@ __device__ __forceinline__ void sweep_block_rows(const ulonglong2* tp, int b, co
     const float bm = fminf(fmin3(fmin3(fmin3(gm[q][0], gm[q][1], gm[q][2]), gm[q][3], gm[q][4]), gm[q][5], gm[q][6]),
                            gm[q][7]);
     const unsigned pk = (__float_as_uint(bm) & 0xffffffc0u) | (unsigned)b;
-    if (pk < best[q]) {
+    if constexpr (FIRST) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) gbest[q][i] = gm[q][i];
+      second[q] = 0xffffffffu;
+      best[q] = pk;
+    } else {
+      if (pk < best[q]) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) gbest[q][i] = gm[q][i];
+      }
+      second[q] = min(second[q], max(best[q], pk));
+      best[q] = min(best[q], pk);
     }
-    second[q] = min(second[q], max(best[q], pk));
-    best[q] = min(best[q], pk);
   }
 }
 
@@ -426,13 +435,16 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
         f32x2 qxx[R], qyy[R];
 #pragma unroll
         for (int q = 0; q < R; ++q) {
-          best[q] = second[q] = 0xffffffffu;
-#pragma unroll
-          for (int g = 0; g < 8; ++g) gbest[q][g] = kInfF;
           qxx[q] = pack2(fqx[q], fqx[q]); qyy[q] = pack2(fqy[q], fqy[q]);
           a_bound[q] = fmaxf(fabsf(fqx[q]), fabsf(fqy[q])) * (1.0f + 4.0f * kU) + tmax;
         }
-        unsigned done_lo = 0u, done_hi = 0u;
+        unsigned done_lo = m_lo, done_hi = m_hi;
+        {   // the first block of the row (the seeds are never empty: a scan has at least one block)
+          const int b0 = m_lo ? __ffs((int)m_lo) - 1 : 32 + __ffs((int)m_hi) - 1;
+          if (m_lo) m_lo &= m_lo - 1u; else m_hi &= m_hi - 1u;
+          tiles += (unsigned)R;
+          sweep_block_rows<R, true>(tp, b0, qxx, qyy, best, second, gbest);
+        }
 #pragma unroll 1
         for (int phase = 0;; ++phase) {
           done_lo |= m_lo; done_hi |= m_hi;
