@@ -445,16 +445,41 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
           tiles += (unsigned)R;
           sweep_block_rows<R, true>(tp, b0, qxx, qyy, best, second, gbest);
         }
-#pragma unroll 1
-        for (int phase = 0;; ++phase) {
-          done_lo |= m_lo; done_hi |= m_hi;
-          // A block admitted by the ROW's bound (phase 1: it does not overlap the row box) is swept only if
-          // at least one lane's OWN point-to-box bound is within that lane's threshold: the bound is the
-          // candidate arithmetic on a degenerate box, so a block refused here holds no target with
-          // d32 <= thr(q) for any query of the row -- typically the neighbours of the overlapping blocks,
-          // which only the queries at the end of the row can reach.
+        // the other seeds: blocks that overlap the row box (or, with PRUNE off, every block)
+        while (m_lo) {
+          const int b = __ffs((int)m_lo) - 1;
+          m_lo &= m_lo - 1u;
+          tiles += (unsigned)R;
+          sweep_block_rows<R>(tp, b, qxx, qyy, best, second, gbest);
+        }
+        while (m_hi) {
+          const int b = 32 + __ffs((int)m_hi) - 1;
+          m_hi &= m_hi - 1u;
+          tiles += (unsigned)R;
+          sweep_block_rows<R>(tp, b, qxx, qyy, best, second, gbest);
+        }
+        // the threshold the resolution uses (final once no further block is swept)
+        auto thresholds = [&]() -> float {
+          float thr_max = 0.f;
+#pragma unroll
+          for (int q = 0; q < R; ++q) {
+            thr[q] = candidate_threshold(__uint_as_float(best[q] & 0xffffffc0u), a_bound[q], kTruncRel);
+            thr_max = fmaxf(thr_max, thr[q]);
+          }
+          return thr_max;
+        };
+        const float thr_seed = thresholds();
+        if constexpr (PRUNE) {
+          // the other blocks that can still hold a candidate of any query of this row: within the row's
+          // bound, and then only if at least one lane's OWN point-to-box bound is within that lane's
+          // threshold (the candidate arithmetic on a degenerate box: a block refused here holds no target
+          // with d32 <= thr(q) for any query of the row) -- typically the neighbours of the overlapping
+          // blocks, which only the queries at the ends of the row can reach
+          const float bound = redux_maxf(thr_seed);
+          m_lo = __ballot_sync(full, !(lb0 > bound)) & vmask_lo & ~done_lo;
+          m_hi = __ballot_sync(full, !(lb1 > bound)) & vmask_hi & ~done_hi;
+          bool swept_more = false;
           auto admitted = [&](int b) -> bool {
-            if (!PRUNE || phase == 0) return true;
             const float4 box = bb[b];
             bool need = false;
 #pragma unroll
@@ -466,6 +491,7 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
             const int b = __ffs((int)m_lo) - 1;
             m_lo &= m_lo - 1u;
             if (!admitted(b)) continue;
+            swept_more = true;
             tiles += (unsigned)R;
             sweep_block_rows<R>(tp, b, qxx, qyy, best, second, gbest);
           }
@@ -473,22 +499,11 @@ __global__ void __launch_bounds__(W * 32, MINB) icp2d_rows_kernel(const RunParam
             const int b = 32 + __ffs((int)m_hi) - 1;
             m_hi &= m_hi - 1u;
             if (!admitted(b)) continue;
+            swept_more = true;
             tiles += (unsigned)R;
             sweep_block_rows<R>(tp, b, qxx, qyy, best, second, gbest);
           }
-          // the threshold the resolution uses (final once no further block is swept)
-          float thr_max = 0.f;
-#pragma unroll
-          for (int q = 0; q < R; ++q) {
-            thr[q] = candidate_threshold(__uint_as_float(best[q] & 0xffffffc0u), a_bound[q], kTruncRel);
-            thr_max = fmaxf(thr_max, thr[q]);
-          }
-          if (!PRUNE || phase == 1) break;
-          // the other blocks that can still hold a candidate of any query of this row
-          const float bound = redux_maxf(thr_max);
-          m_lo = __ballot_sync(full, !(lb0 > bound)) & vmask_lo & ~done_lo;
-          m_hi = __ballot_sync(full, !(lb1 > bound)) & vmask_hi & ~done_hi;
-          if ((m_lo | m_hi) == 0u) break;
+          if (swept_more) thresholds();     // best may have improved: the final thresholds
         }
 
         // exact resolution in float64
