@@ -8,9 +8,13 @@
  * stated otherwise), including the workspace; the entries never allocate device
  * memory and are re-entrant.  All launches are asynchronous on the given CUDA
  * stream (pass a cudaStream_t cast to void*; NULL = the legacy default stream).
- * Two documented exceptions: b200icp_run_host takes HOST pointers and owns a
- * per-device arena and streams (freed by b200icp_host_release), and
- * b200icp_ogm_build keeps one auxiliary stream per device.  Functions return 0 or a negative
+ * Documented exceptions: the HOST entries (b200icp_run_host*, b200icp_run_pair_host,
+ * b200icp_submit_host_ranges / b200icp_wait_host) take host pointers and own grow-only
+ * per-device arenas and streams (freed by b200icp_host_release; calls on one device are
+ * serialised, two submitted calls may be in flight); b200icp_host_alloc / _free hand out
+ * page-locked host memory; b200icp_run_static uses a fixed scratch array inside the
+ * library's device image instead of a caller workspace; b200icp_ogm_build keeps one
+ * auxiliary stream per device.  Functions return 0 or a negative
  * B200ICP_ERR_* code; per-pair anomalies are reported in `status_out`, never
  * as a call failure, because the reference does not raise on them either.
  */
